@@ -1,0 +1,83 @@
+// kernels.h -- host-visible launch interface of the CUDA kernels (internal to the .so).
+#pragma once
+#include "common.cuh"
+
+namespace epv {
+
+constexpr int MH_THREADS = 128;                 // groups (of 3 sites) per tile
+constexpr int MH_TILE_SITES = 3*MH_THREADS;
+
+struct PassArgs {
+  ModelParams mp;
+  PathView in;                // snapshot read by every update of this colour pass
+  uint32_t *off_out;          // rebuilt CSR (ping-pong partner), same pitch / jbase
+  double *jmp_out;
+  const uint64_t *jcap;       // [n_branches] capacity of each branch's jump slice
+  uint8_t *state;             // in place: only the updated site's own bits change
+  int W;
+  TreeDev tree;
+  double *tri_llh;            // in place: an update writes [s-1, s+1]
+  uint64_t n_sites;           // local sites (shard + halos)
+  uint64_t upd_lo, upd_hi;    // local site range this context updates
+  int64_t global0;            // global index of local site 0
+  uint64_t n_global;
+  int colour;
+  uint64_t seed;
+  uint32_t sweep;
+  // single-pass chained scan (decoupled look-back) state
+  unsigned long long *desc;   // [n_branches * n_tiles]
+  uint32_t n_tiles;
+  uint32_t epoch;
+  uint32_t *ticket;
+  uint32_t ticket_base;
+  // overflow scratch for proposals longer than the per-thread buffer
+  double *scratch;
+  uint32_t *scratch_ctr;
+  uint32_t scratch_slots, scratch_cap;
+  unsigned *err;
+  unsigned long long *n_accept;
+};
+
+void launch_mh_pass(const PassArgs &a, cudaStream_t st);
+size_t mh_pass_smem_bytes(int n_nodes);
+
+void launch_tri_llh(const ModelParams &mp, const PathView &pv, const uint8_t *state, int W,
+                    const TreeDev &tree, uint64_t n_sites, double *tri_llh,
+                    cudaStream_t st);
+
+struct DebugOut {
+  unsigned long long *n_intervals, *seg_off, *trip0, *trip1;
+  double *rate0, *rate1, *len, *p, *q, *root_p0, *logp;
+  unsigned long long cap;
+};
+void launch_site_debug(const ModelParams &mp, const PathView &pv, const uint8_t *state,
+                       int W, const TreeDev &tree, uint64_t site, const DebugOut &out,
+                       cudaStream_t st);
+void launch_end_cond(double r0, double r1, int a, int b, double T, uint64_t seed,
+                     uint64_t n, uint64_t cap, uint32_t *n_jumps, double *jumps,
+                     cudaStream_t st);
+
+// J/D sufficient statistics: acc = [n_branches][24] doubles per context
+// (8 D sums, 8 J counts, 8 event-free row counts are folded on device).
+void launch_suffstats(const PathView &pv, const uint8_t *state, int W, const TreeDev &tree,
+                      uint64_t n_sites, uint64_t lo, uint64_t hi, double *J, double *D,
+                      unsigned long long *scratch, cudaStream_t st, int sm_count);
+size_t suffstats_scratch_bytes(int n_nodes, int sm_count);
+void launch_llh_grad(const double *J, const double *D, int n_nodes, const double *rates_dev,
+                     double *out9, cudaStream_t st);
+void launch_axpy_stats(double *J_sum, double *D_sum, const double *J, const double *D, int n,
+                       cudaStream_t st);
+
+void launch_scale_jumps(double *jmp, const uint64_t *jbase, const uint32_t *off,
+                        uint64_t off_pitch, uint64_t n_sites, int n_branches,
+                        const double *scale, cudaStream_t st);
+
+// host exchange format <-> device layout
+void launch_import(const uint8_t *h_init, const unsigned long long *h_off,
+                   uint64_t n_sites, int n_nodes, uint32_t *off, uint64_t off_pitch,
+                   uint8_t *state, int W, cudaStream_t st);
+void launch_export(const uint32_t *off, uint64_t off_pitch, const uint8_t *state, int W,
+                   uint64_t n_sites, int n_nodes, const uint64_t *jprefix,
+                   uint8_t *h_init, unsigned long long *h_off, cudaStream_t st);
+
+}  // namespace epv

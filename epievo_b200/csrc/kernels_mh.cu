@@ -1,0 +1,205 @@
+// kernels_mh.cu -- the Metropolis-Hastings colour-pass kernel.
+//
+// One launch updates every site s == colour (mod 3) of the shard
+// (SingleSiteSampler::single_iteration, SingleSiteSampler.cpp:538-548, re-ordered
+// into stride-3 colour classes: updates of s and s+3 touch disjoint data) AND rebuilds
+// the per-branch CSR in the ping-pong buffer in the same pass:
+//   phase 1  one thread per group of 3 sites runs mh_site() for the group's target
+//   phase 2  per branch, the new row lengths of the tile are summed per thread
+//   phase 3  per branch, one warp scans the tile and obtains the tile's base offset
+//            with a single-pass chained scan (decoupled look-back) across tiles
+//   phase 4  every thread writes its 3 rows' offsets and jump times to the new CSR
+// so each pass reads the old CSR once and writes the new one once; there is no
+// staging buffer and no separate scan/compaction kernel.
+#include "kernels.h"
+#include "mh_site2.cuh"
+
+namespace epv {
+
+namespace {
+
+constexpr unsigned long long FLAG_AGG = 1ull << 32, FLAG_INC = 2ull << 32;
+
+__device__ __forceinline__ unsigned long long
+ld_desc(const unsigned long long *p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void
+st_desc(unsigned long long *p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
+}
+
+// Exclusive prefix of this tile's total for one branch; executed by a full warp.
+__device__ __forceinline__ uint32_t
+tile_base(unsigned long long *desc, uint32_t tile, uint32_t epoch, uint32_t total,
+          int lane) {
+  const unsigned long long tag = (unsigned long long)epoch << 34;
+  if (tile == 0) {
+    if (lane == 0) st_desc(desc, tag | FLAG_INC | total);
+    return 0;
+  }
+  if (lane == 0) st_desc(desc + tile, tag | FLAG_AGG | total);
+  uint32_t base = 0;
+  int64_t look = (int64_t)tile - 1;
+  for (;;) {
+    const int64_t idx = look - lane;
+    unsigned long long d;
+    bool ready;
+    do {
+      d = idx >= 0 ? ld_desc(desc + idx) : (tag | FLAG_INC);
+      ready = (d >> 34) == epoch && (d & (FLAG_AGG | FLAG_INC)) != 0;
+    } while (__any_sync(0xffffffffu, !ready));
+    const unsigned inc = __ballot_sync(0xffffffffu, (d & FLAG_INC) != 0);
+    const int first = inc ? __ffs(inc) - 1 : 32;
+    uint32_t v = lane <= first ? (uint32_t)d : 0u;
+    v = warp_sum(v);
+    base += v;
+    if (inc) break;
+    look -= 32;
+  }
+  if (lane == 0) st_desc(desc + tile, tag | FLAG_INC | (base + total));
+  return base;
+}
+
+template <int MAXN, int MAXJ>
+__global__ void __launch_bounds__(MH_THREADS)
+mh_pass_kernel(const PassArgs a) {
+  extern __shared__ uint32_t s_len[];            // [n_branches][MH_THREADS]
+  __shared__ ModelParams s_mp;
+  __shared__ uint32_t s_tile;
+  __shared__ int s_fail;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int n_br = a.tree.n_nodes - 1;
+  if (t == 0) {
+    s_tile = atomicAdd(a.ticket, 1u) - a.ticket_base;
+    s_fail = 0;
+    s_mp = a.mp;
+  }
+  __syncthreads();
+  const uint32_t tile = s_tile;
+  const uint64_t g = (uint64_t)tile*MH_THREADS + t;     // group of sites 3g..3g+2
+  const uint64_t s0 = 3*g;
+  const uint64_t st = s0 + a.colour;                    // the group's target site
+  const int64_t gsite = a.global0 + (int64_t)st;
+
+  // ---- phase 1: the update -------------------------------------------------------
+  double q[2*MAXN];
+  double pj_local[MAXJ];
+  uint16_t pn[MAXN];
+  uint8_t pend[MAXN];
+  Proposal pr; pr.pj = pj_local; pr.cap = MAXJ; pr.pn = pn; pr.pend = pend;
+  int accepted = 0, total = 0;
+  if (st >= a.upd_lo && st < a.upd_hi && gsite >= 1 && gsite + 1 < (int64_t)a.n_global) {
+    SiteCtx c; c.pv = a.in; c.state = a.state; c.W = a.W; c.tree = a.tree; c.site = st;
+    int r = mh_site(s_mp, c, a.state, a.tri_llh, a.seed, a.sweep, (uint64_t)gsite,
+                    a.n_global, q, pr, total);
+    if (r == -1) {        // proposal longer than the per-thread buffer: global scratch
+      const uint32_t slot = atomicAdd(a.scratch_ctr, 1u);
+      if (slot >= a.scratch_slots) { atomicOr(a.err, ERR_SCRATCH_SLOTS); r = 0; }
+      else {
+        pr.pj = a.scratch + (uint64_t)slot*a.scratch_cap; pr.cap = (int)a.scratch_cap;
+        r = mh_site(s_mp, c, a.state, a.tri_llh, a.seed, a.sweep, (uint64_t)gsite,
+                    a.n_global, q, pr, total);
+        if (r == -1) { atomicOr(a.err, ERR_SCRATCH_SIZE); r = 0; }
+      }
+    }
+    if (r == -2) { atomicOr(a.err, ERR_SAMPLER_STUCK); r = 0; }
+    accepted = r;
+  }
+  const unsigned acc_mask = __ballot_sync(0xffffffffu, accepted);
+  if (lane == 0 && acc_mask) atomicAdd(a.n_accept, (unsigned long long)__popc(acc_mask));
+
+  // ---- phase 2: new row lengths, summed per thread ------------------------------
+  for (int bi = 0; bi < n_br; ++bi) {
+    uint32_t sum = 0;
+    if (s0 < a.n_sites) {
+      const uint32_t *o = a.in.off + (uint64_t)bi*a.in.off_pitch;
+      const uint64_t hi = min(s0 + 3, a.n_sites);
+      sum = o[hi] - o[s0];
+      if (accepted) sum = sum - (o[st + 1] - o[st]) + pn[bi + 1];
+    }
+    s_len[bi*MH_THREADS + t] = sum;
+  }
+  __syncthreads();
+
+  // ---- phase 3: per-branch tile scan + chained look-back ------------------------
+  for (int bi = warp; bi < n_br; bi += MH_THREADS/32) {
+    uint32_t *row = s_len + bi*MH_THREADS;
+    uint32_t v[MH_THREADS/32], mine = 0;
+#pragma unroll
+    for (int k = 0; k < MH_THREADS/32; ++k) { v[k] = row[lane*(MH_THREADS/32) + k]; mine += v[k]; }
+    uint32_t incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t up = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += up;
+    }
+    const uint32_t tot = __shfl_sync(0xffffffffu, incl, 31);
+    const uint32_t base = tile_base(a.desc + (uint64_t)bi*a.n_tiles, tile, a.epoch, tot, lane);
+    if (lane == 0 && (uint64_t)base + tot > a.jcap[bi]) {
+      atomicOr(a.err, ERR_JUMP_CAPACITY);
+      s_fail = 1;
+    }
+    uint32_t run = base + incl - mine;
+#pragma unroll
+    for (int k = 0; k < MH_THREADS/32; ++k) { row[lane*(MH_THREADS/32) + k] = run; run += v[k]; }
+    if (tile == a.n_tiles - 1 && lane == 31)
+      a.off_out[(uint64_t)bi*a.in.off_pitch + a.n_sites] = base + tot;
+  }
+  __syncthreads();
+  if (s_fail || s0 >= a.n_sites) return;
+
+  // ---- phase 4: write the rebuilt rows ---------------------------------------------
+  int poff = 0;
+  for (int bi = 0; bi < n_br; ++bi) {
+    const uint32_t *o = a.in.off + (uint64_t)bi*a.in.off_pitch;
+    uint32_t *oo = a.off_out + (uint64_t)bi*a.in.off_pitch;
+    const double *src_base = a.in.jmp + a.in.jbase[bi];
+    double *dst_base = a.jmp_out + a.in.jbase[bi];
+    uint32_t w = s_len[bi*MH_THREADS + t];
+    const uint64_t hi = min(s0 + 3, a.n_sites);
+    for (uint64_t s = s0; s < hi; ++s) {
+      oo[s] = w;
+      if (accepted && s == st) {
+        const int n = pn[bi + 1];
+        for (int k = 0; k < n; ++k) dst_base[w + k] = pr.pj[poff + k];
+        w += n;
+      }
+      else {
+        const uint32_t b = o[s], e = o[s + 1];
+        for (uint32_t k = b; k < e; ++k) dst_base[w + (k - b)] = src_base[k];
+        w += e - b;
+      }
+    }
+    poff += pn[bi + 1];
+  }
+}
+
+}  // namespace
+
+size_t
+mh_pass_smem_bytes(int n_nodes) {
+  return (size_t)(n_nodes - 1)*MH_THREADS*sizeof(uint32_t);
+}
+
+template <int MAXN, int MAXJ>
+static void
+launch_t(const PassArgs &a, cudaStream_t st) {
+  const size_t smem = mh_pass_smem_bytes(a.tree.n_nodes);
+  cudaFuncSetAttribute(mh_pass_kernel<MAXN, MAXJ>,
+                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  mh_pass_kernel<MAXN, MAXJ><<<a.n_tiles, MH_THREADS, smem, st>>>(a);
+}
+
+void
+launch_mh_pass(const PassArgs &a, cudaStream_t st) {
+  const int n = a.tree.n_nodes;
+  if (n <= 8) launch_t<8, 16>(a, st);
+  else if (n <= 16) launch_t<16, 32>(a, st);
+  else if (n <= 64) launch_t<64, 64>(a, st);
+  else launch_t<256, 128>(a, st);
+}
+
+}  // namespace epv

@@ -1,0 +1,231 @@
+// kernels_stats.cu -- J/D triplet sufficient statistics, log-likelihood / gradient,
+// jump-time rescale and the host-format import/export kernels.
+#include "kernels.h"
+#include "rows.cuh"
+
+namespace epv {
+
+namespace {
+
+constexpr int SS_THREADS = 256;
+
+// Per-branch J/D over every interior site of the shard
+// (get_sufficient_statistics, ParamEstimation.cpp:92-114, built on
+// add_sufficient_statistics, Path.cpp:267-301).  Rows whose three paths have no jumps
+// (the vast majority) only contribute tot_time to D[triplet]: they are COUNTED per
+// triplet with warp match + one shared-memory integer atomic per distinct triplet;
+// rows with events take the three-way merge and add into shared-memory accumulators.
+// acc layout per branch: [0..8) D partial sums (double), [8..16) J counts, [16..24)
+// event-free row counts (both uint64 bit patterns in the same array).
+__global__ void __launch_bounds__(SS_THREADS)
+suffstats_kernel(const PathView pv, const uint8_t *state, int W, int n_br,
+                 uint64_t lo, uint64_t hi, unsigned long long *acc) {
+  extern __shared__ unsigned long long s_raw[];
+  double *s_D = reinterpret_cast<double *>(s_raw);               // [n_br*8]
+  unsigned *s_J = reinterpret_cast<unsigned *>(s_raw + n_br*8);   // [n_br*8]
+  unsigned *s_C = s_J + n_br*8;                                   // [n_br*8]
+  for (int i = threadIdx.x; i < n_br*8; i += SS_THREADS) { s_D[i] = 0.0; s_J[i] = 0; s_C[i] = 0; }
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const uint64_t span = hi - lo;
+  const uint64_t n_iter = (span + (uint64_t)gridDim.x*SS_THREADS - 1)/((uint64_t)gridDim.x*SS_THREADS);
+  for (uint64_t it = 0; it < n_iter; ++it) {
+    const uint64_t s = lo + (it*gridDim.x + blockIdx.x)*SS_THREADS + threadIdx.x;
+    const bool live = s < hi;
+    for (int bi = 0; bi < n_br; ++bi) {
+      int key = 8;
+      Row L, M, R;
+      if (live) {
+        L = load_row(pv, state, W, bi, s - 1);
+        M = load_row(pv, state, W, bi, s);
+        R = load_row(pv, state, W, bi, s + 1);
+        if ((L.n | M.n | R.n) == 0) key = L.init*4 + M.init*2 + R.init;
+      }
+      const unsigned peers = __match_any_sync(0xffffffffu, key);
+      if (key < 8) {
+        if (lane == __ffs(peers) - 1) atomicAdd(&s_C[bi*8 + key], (unsigned)__popc(peers));
+      }
+      else if (live) {
+        int trip = L.init*4 + M.init*2 + R.init, i = 0, j = 0, k = 0;
+        double prev = 0.0;
+        const double INF = __longlong_as_double(0x7ff0000000000000LL);
+        for (;;) {
+          if (i >= L.n && j >= M.n && k >= R.n) break;
+          const double tl = i < L.n ? L.ptr[i] : INF;
+          const double tm = j < M.n ? M.ptr[j] : INF;
+          const double tr = k < R.n ? R.ptr[k] : INF;
+          double tn; int flip;
+          if (tl < fmin(tm, tr)) { tn = tl; flip = 4; ++i; }
+          else if (tm < tr) { tn = tm; flip = 2; ++j; atomicAdd(&s_J[bi*8 + trip], 1u); }
+          else { tn = tr; flip = 1; ++k; }
+          atomicAdd(&s_D[bi*8 + trip], tn - prev);
+          prev = tn; trip ^= flip;
+        }
+        // final segment: tot_time - prev; tot_time is added on the host side of the
+        // fold as (count of rows ending in this triplet) -- keep it exact here instead
+        atomicAdd(&s_D[bi*8 + trip], -prev);
+        atomicAdd(&s_C[bi*8 + trip], 1u);
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < n_br*8; i += SS_THREADS) {
+    const int bi = i >> 3, t = i & 7;
+    if (s_D[i] != 0.0) atomicAdd(reinterpret_cast<double *>(acc) + bi*24 + t, s_D[i]);
+    if (s_J[i]) atomicAdd(acc + bi*24 + 8 + t, (unsigned long long)s_J[i]);
+    if (s_C[i]) atomicAdd(acc + bi*24 + 16 + t, (unsigned long long)s_C[i]);
+  }
+}
+
+// D[b][t] = partial + count*tot_time[b];  J[b][t] = count.  Row 0 (root) is zero.
+__global__ void
+suffstats_fold_kernel(const unsigned long long *acc, const double *branch, int n_nodes,
+                      double *J, double *D) {
+  const int i = blockIdx.x*blockDim.x + threadIdx.x;
+  if (i >= n_nodes*8) return;
+  const int b = i >> 3, t = i & 7;
+  if (b == 0) { J[i] = 0.0; D[i] = 0.0; return; }
+  const unsigned long long *a = acc + (b - 1)*24;
+  D[i] = __longlong_as_double((long long)a[t]) + (double)a[16 + t]*branch[b];
+  J[i] = (double)a[8 + t];
+}
+
+struct Rates8 { double r[8]; };
+
+// log_likelihood (ParamEstimation.cpp:131-143) and get_gradient (:147-194) on J/D
+// collapsed over branches (:299-315).  out = [llh, g0..g7].
+__global__ void
+llh_grad_kernel(const double *Jb, const double *Db, int n_nodes, Rates8 R, double *out) {
+  if (threadIdx.x != 0) return;
+  double J[8], D[8];
+  for (int t = 0; t < 8; ++t) { J[t] = 0.0; D[t] = 0.0; }
+  for (int b = 1; b < n_nodes; ++b)
+    for (int t = 0; t < 8; ++t) { J[t] += Jb[b*8 + t]; D[t] += Db[b*8 + t]; }
+  double ll = 0.0;
+  for (int t = 0; t < 8; ++t) ll += J[t]*log(R.r[t]) - D[t]*R.r[t];
+  const double *r = R.r;
+  const double f = J[7] - D[7]*r[7];
+  double g[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  g[0] = J[0] - D[0]*r[0] + f;
+  g[2] = J[2] - D[2]*r[2] - f;
+  g[1] = J[1] + J[4] - (D[1] + D[4])*r[1] - 2*f;
+  g[4] = g[1];
+  g[3] = J[3] + J[6] - (D[3] + D[6])*r[3] + 2*f;
+  g[6] = g[3];
+  g[5] = J[5] - D[5]*r[5] + f;
+  out[0] = ll;
+  for (int t = 0; t < 8; ++t) out[1 + t] = g[t];
+}
+
+__global__ void
+axpy_kernel(double *Js, double *Ds, const double *J, const double *D, int n) {
+  const int i = blockIdx.x*blockDim.x + threadIdx.x;
+  if (i < n) { Js[i] += J[i]; Ds[i] += D[i]; }
+}
+
+// scale_jump_times (ParamEstimation.cpp:369-380): jump *= new_branch/tot_time.
+__global__ void __launch_bounds__(256)
+scale_kernel(double *jmp, const uint64_t *jbase, const uint32_t *off, uint64_t pitch,
+             uint64_t n_sites, const double *scale) {
+  const int bi = blockIdx.y;
+  const uint64_t n = off[(uint64_t)bi*pitch + n_sites];
+  double *p = jmp + jbase[bi];
+  const double sc = scale[bi + 1];
+  for (uint64_t k = (uint64_t)blockIdx.x*blockDim.x + threadIdx.x; k < n;
+       k += (uint64_t)gridDim.x*blockDim.x)
+    p[k] *= sc;
+}
+
+__global__ void __launch_bounds__(256)
+import_kernel(const uint8_t *h_init, const unsigned long long *h_off, uint64_t n_sites,
+              int n_nodes, uint32_t *off, uint64_t pitch, uint8_t *state, int W) {
+  const uint64_t s = (uint64_t)blockIdx.x*blockDim.x + threadIdx.x;
+  if (s > n_sites) return;
+  for (int b = 1; b < n_nodes; ++b)
+    off[(uint64_t)(b - 1)*pitch + s] =
+      (uint32_t)(h_off[(uint64_t)b*n_sites + s] - h_off[(uint64_t)b*n_sites]);
+  if (s == n_sites) return;
+  for (int w = 0; w < W; ++w) {
+    unsigned bits = 0;
+    for (int k = 0; k < 8; ++k) {
+      const int v = w*8 + k;
+      if (v >= 1 && v < n_nodes) bits |= (unsigned)(h_init[(uint64_t)v*n_sites + s] != 0) << k;
+    }
+    state[s*W + w] = (uint8_t)bits;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+export_kernel(const uint32_t *off, uint64_t pitch, const uint8_t *state, int W,
+              uint64_t n_sites, int n_nodes, const uint64_t *jprefix, uint8_t *h_init,
+              unsigned long long *h_off) {
+  const uint64_t s = (uint64_t)blockIdx.x*blockDim.x + threadIdx.x;
+  if (s >= n_sites) return;
+  h_init[s] = 0; h_off[s] = 0;
+  for (int b = 1; b < n_nodes; ++b) {
+    h_init[(uint64_t)b*n_sites + s] = (uint8_t)state_bit(state, W, s, b);
+    h_off[(uint64_t)b*n_sites + s] = jprefix[b - 1] + off[(uint64_t)(b - 1)*pitch + s];
+  }
+  if (s == 0) h_off[(uint64_t)n_nodes*n_sites] = jprefix[n_nodes - 1];
+}
+
+}  // namespace
+
+size_t
+suffstats_scratch_bytes(int n_nodes, int) { return (size_t)(n_nodes - 1)*24*8; }
+
+void
+launch_suffstats(const PathView &pv, const uint8_t *state, int W, const TreeDev &tree,
+                 uint64_t, uint64_t lo, uint64_t hi, double *J, double *D,
+                 unsigned long long *scratch, cudaStream_t st, int sm_count) {
+  const int n_br = tree.n_nodes - 1;
+  cudaMemsetAsync(scratch, 0, (size_t)n_br*24*8, st);
+  if (hi > lo) {
+    const uint64_t want = (hi - lo + SS_THREADS - 1)/SS_THREADS;
+    const unsigned blocks = (unsigned)(want < (uint64_t)sm_count*8 ? want : (uint64_t)sm_count*8);
+    const size_t smem = (size_t)n_br*8*(8 + 4 + 4);
+    cudaFuncSetAttribute(suffstats_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    suffstats_kernel<<<blocks, SS_THREADS, smem, st>>>(pv, state, W, n_br, lo, hi, scratch);
+  }
+  suffstats_fold_kernel<<<(tree.n_nodes*8 + 127)/128, 128, 0, st>>>(scratch, tree.branch,
+                                                                   tree.n_nodes, J, D);
+}
+
+void
+launch_llh_grad(const double *J, const double *D, int n_nodes, const double *rates,
+                double *out9, cudaStream_t st) {
+  Rates8 R;
+  for (int i = 0; i < 8; ++i) R.r[i] = rates[i];
+  llh_grad_kernel<<<1, 32, 0, st>>>(J, D, n_nodes, R, out9);
+}
+
+void
+launch_axpy_stats(double *Js, double *Ds, const double *J, const double *D, int n,
+                  cudaStream_t st) {
+  axpy_kernel<<<(n + 127)/128, 128, 0, st>>>(Js, Ds, J, D, n);
+}
+
+void
+launch_scale_jumps(double *jmp, const uint64_t *jbase, const uint32_t *off, uint64_t pitch,
+                   uint64_t n_sites, int n_branches, const double *scale, cudaStream_t st) {
+  dim3 grid(592, n_branches);
+  scale_kernel<<<grid, 256, 0, st>>>(jmp, jbase, off, pitch, n_sites, scale);
+}
+
+void
+launch_import(const uint8_t *h_init, const unsigned long long *h_off, uint64_t n_sites,
+              int n_nodes, uint32_t *off, uint64_t pitch, uint8_t *state, int W,
+              cudaStream_t st) {
+  import_kernel<<<(unsigned)((n_sites + 256)/256), 256, 0, st>>>(h_init, h_off, n_sites,
+                                                                 n_nodes, off, pitch, state, W);
+}
+
+void
+launch_export(const uint32_t *off, uint64_t pitch, const uint8_t *state, int W,
+              uint64_t n_sites, int n_nodes, const uint64_t *jprefix, uint8_t *h_init,
+              unsigned long long *h_off, cudaStream_t st) {
+  export_kernel<<<(unsigned)((n_sites + 255)/256), 256, 0, st>>>(off, pitch, state, W, n_sites,
+                                                                 n_nodes, jprefix, h_init, h_off);
+}
+
+}  // namespace epv

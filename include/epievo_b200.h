@@ -1,0 +1,179 @@
+/* epievo_b200.h -- C-ABI of the B200-native MCMC / sufficient-statistics hot path.
+ *
+ * Drop-in boundary for the reference's (smithlabcode/epievo @ 6e0525a) C++ API of
+ * this path.  The reference has no FFI layer; what its three programs and one
+ * harness call directly is listed beside each entry point ("replaces ..."), with
+ * paths relative to the reference's src/libepievo/.  The C++ shim that keeps the
+ * reference's class and function signatures on top of these calls is
+ * epievo_b200/host/epievo_b200.hpp; INTEGRATION.md shows how a maintainer links it.
+ *
+ * Conventions
+ *  - every call returns 0 on success, non-zero on failure; epv_last_error() then
+ *    holds the message (the shim rethrows it as std::runtime_error, the reference's
+ *    error convention, e.g. prog/epievo_est_params_histories.cpp:296-299);
+ *  - buffers passed in are caller-owned and only read during the call; output
+ *    buffers are caller-allocated;
+ *  - one host thread drives one context; one context drives one GPU;
+ *  - there is NO CPU fallback: without a CUDA device epv_create fails.
+ *
+ * Path exchange format ("node-major CSR"), mirroring vector<vector<Path>>
+ * (Path.hpp:33-57) as transposed by the callers
+ * (prog/epievo_est_params_histories.cpp:180-192):
+ *    init_state : uint8  [n_nodes * n_sites]       row = node*n_sites + site
+ *    row_off    : uint64 [n_nodes * n_sites + 1]   offsets into jumps
+ *    jumps      : double [row_off[n_nodes*n_sites]]
+ *    tot_time   : double [n_nodes]                 Path::tot_time of the node's rows
+ * Node 0 (root) rows are empty; the root state of site s is init_state of node 1
+ * (SingleSiteSampler.cpp:409-410, 502-504).
+ */
+#ifndef EPIEVO_B200_H
+#define EPIEVO_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct epv_ctx epv_ctx;
+
+#define EPV_N_TRIPLETS 8
+
+/* ---- context ------------------------------------------------------------------ */
+/* device: CUDA device ordinal.  Fails (no fallback) when CUDA is unavailable. */
+int  epv_create(epv_ctx **ctx, int device);
+void epv_destroy(epv_ctx *ctx);
+const char *epv_last_error(const epv_ctx *ctx);
+/* Run all subsequent work on this cudaStream_t (0 = the context's own stream). */
+int  epv_set_stream(epv_ctx *ctx, void *cuda_stream);
+int  epv_synchronize(epv_ctx *ctx);
+
+/* ---- inputs ---------------------------------------------------------------------- */
+/* replaces TreeHelper (TreeHelper.hpp:38-57): preorder arrays, branch b = edge above
+ * node b, branches[0] ignored. */
+int epv_set_tree(epv_ctx *ctx, uint64_t n_nodes, const uint64_t *subtree_sizes,
+                 const uint64_t *parent_ids, const double *branches);
+/* replaces the EpiEvoModel fields the path reads (EpiEvoModel.hpp:32-65):
+ * triplet_rates[8] (index l*4+m*2+r) and the horizontal 2x2 T (row-major). */
+int epv_set_model(epv_ctx *ctx, const double *triplet_rates, const double *T);
+
+/* Sharding (one context per GPU): this context holds global sites
+ * [site_begin - halo_lo, site_end + halo_hi) of an n_global-site problem; only sites
+ * in [site_begin, site_end) are updated / counted here.  site_begin must be a
+ * multiple of 3.  Default (never called): the whole problem, no halo. */
+int epv_set_shard(epv_ctx *ctx, uint64_t n_global, uint64_t site_begin,
+                  uint64_t site_end, uint64_t halo_lo, uint64_t halo_hi);
+
+/* host paths -> device CSR (replaces handing vector<vector<Path>>& to the sampler).
+ * n_sites counts the rows actually passed (shard + halos). */
+int epv_upload_paths(epv_ctx *ctx, uint64_t n_sites, uint64_t n_nodes,
+                     const uint8_t *init_state, const uint64_t *row_off,
+                     const double *jumps, const double *tot_time);
+/* device CSR -> host.  Call epv_paths_size first to size the buffers. */
+int epv_paths_size(epv_ctx *ctx, uint64_t *n_sites, uint64_t *n_nodes,
+                   uint64_t *n_jumps);
+int epv_download_paths(epv_ctx *ctx, uint8_t *init_state, uint64_t *row_off,
+                       double *jumps, double *tot_time);
+
+/* ---- the sampler (SingleSiteSampler.hpp:35-81) --------------------------------- */
+/* replaces SingleSiteSampler::reset (SingleSiteSampler.cpp:449-475): caches the
+ * per-site triplet log-likelihoods for the current model and paths. */
+int epv_reset(epv_ctx *ctx);
+/* replaces SingleSiteSampler::single_iteration (SingleSiteSampler.cpp:538-548):
+ * one Metropolis-Hastings update of every interior site, applied in three stride-3
+ * colour passes; randomness is Philox4x32-10 keyed by (seed, sweep_idx, site, node).
+ * n_accepted may be NULL. */
+int epv_sweep(epv_ctx *ctx, uint64_t seed, uint64_t sweep_idx, uint64_t *n_accepted);
+/* replaces SingleSiteSampler::run_mcmc (SingleSiteSampler.cpp:550-598): burn_in
+ * sweeps, then batch x (sweep + per-branch J/D), batch-averaged.  J, D are
+ * [n_nodes*8] (row 0 zero); acc_rate = accepted / (batch*(n_global-2)) over this
+ * shard's sites.  Sweep indices first_sweep .. first_sweep+burn_in+batch-1. */
+int epv_run_mcmc(epv_ctx *ctx, uint64_t burn_in, uint64_t batch, uint64_t seed,
+                 uint64_t first_sweep, double *J, double *D, double *acc_rate);
+/* Same as epv_run_mcmc but leaves J/D sums (not averaged) and the accept count on
+ * the device-side accumulators and returns them raw, so a multi-GPU driver can
+ * all-reduce them before averaging. */
+int epv_run_mcmc_raw(epv_ctx *ctx, uint64_t burn_in, uint64_t batch, uint64_t seed,
+                     uint64_t first_sweep, double *J_sum, double *D_sum,
+                     uint64_t *n_accepted);
+
+/* ---- sufficient statistics, likelihood, gradient -------------------------------- */
+/* replaces get_sufficient_statistics(paths, J, D) per branch
+ * (ParamEstimation.cpp:92-114): J, D are [n_nodes*8], row 0 zero. */
+int epv_suffstats(epv_ctx *ctx, double *J, double *D);
+/* replaces log_likelihood + get_gradient (ParamEstimation.cpp:131-194) evaluated on
+ * the device-resident J/D of the last epv_suffstats / epv_run_mcmc, collapsed over
+ * branches. */
+int epv_llh_grad(epv_ctx *ctx, const double *rates, double *llh, double *grad);
+/* replaces scale_jump_times (ParamEstimation.cpp:369-380): every jump of branch b
+ * is multiplied by new_branches[b]/tot_time[b]; tot_time and the tree's branch
+ * lengths become new_branches. */
+int epv_scale_jump_times(epv_ctx *ctx, const double *new_branches);
+
+/* ---- halo exchange (multi-GPU; see epv_set_shard) -------------------------------- */
+/* Pack the paths of `count` sites starting at local site `first` into a
+ * self-describing blob in DEVICE memory owned by the context; returns its address
+ * and size.  The peer feeds the blob to epv_halo_unpack, which overwrites its own
+ * `count` sites starting at local site `first`.  Blobs never pass through the host. */
+int epv_halo_pack(epv_ctx *ctx, uint64_t first, uint64_t count, int slot,
+                  void **dev_blob, uint64_t *n_bytes);
+int epv_halo_recv_buffer(epv_ctx *ctx, int slot, uint64_t n_bytes, void **dev_blob);
+int epv_halo_unpack(epv_ctx *ctx, uint64_t first, uint64_t count, int slot);
+uint64_t epv_halo_blob_bytes(const epv_ctx *ctx, uint64_t count);
+
+/* ---- deterministic per-site intermediates (parity tests of a2/a3/a4/a7) --------- */
+/* For local site `site`: the neighbour-interval lists of every node
+ * (collect_segment_info, Segment.cpp:35-79), the Felsenstein p/q values (pruning,
+ * SingleSiteSampler.cpp:80-157), the root posterior (:167-176) and the proposal
+ * log-probability of the CURRENT path (proposal_prob, :316-339), computed by the
+ * same device functions the sampler kernel uses.  Returns the interval count in
+ * *n_intervals; fails if it exceeds cap. */
+int epv_site_debug(epv_ctx *ctx, uint64_t site, uint64_t cap, uint64_t *n_intervals,
+                   uint64_t *seg_off, double *rate0, double *rate1, uint64_t *trip0,
+                   uint64_t *trip1, double *len, double *p, double *q,
+                   double *root_p0, double *proposal_logp);
+/* Cached tri_llh of every local site (SingleSiteSampler.cpp:470-474). */
+int epv_get_tri_llh(epv_ctx *ctx, double *tri_llh);
+/* Draw n end-conditioned paths on one interval with the sampler kernel's own device
+ * routine (replaces end_cond_sample_forward_rejection, EndCondSampling.cpp:479-509;
+ * same law, rejection-free): writes the jump count of each draw to n_jumps[n] and
+ * the first `cap` jump times of each to jumps[n*cap]. */
+int epv_end_cond_sample(epv_ctx *ctx, double rate0, double rate1, int start_state,
+                        int end_state, double T, uint64_t seed, uint64_t n,
+                        uint64_t cap, uint32_t *n_jumps, double *jumps);
+
+/* ---- host-side model arithmetic (O(8); no device work) ---------------------------- */
+/* replaces read_model/initialize/scale_triplet_rates (EpiEvoModel.cpp:319-417). */
+void epv_model_from_params(double T00, double T11, double baseline00,
+                           double baseline11, int scale, double *rates, double *T,
+                           double *Q, double *baseline);
+/* replaces EpiEvoModel::rebuild_from_triplet_rates (EpiEvoModel.cpp:420-449). */
+void epv_model_rebuild(const double *rates, double *T, double *Q, double *baseline);
+/* replaces rate_scaling_factor (EpiEvoModel.cpp:158-189). */
+double epv_rate_scaling_factor(const double *rates);
+/* replaces estimate_rates(J, D, model) (ParamEstimation.cpp:337-353): rates in/out. */
+double epv_estimate_rates(uint64_t n_nodes, const double *J, const double *D,
+                          double param_tol, double *rates, double *T,
+                          double *baseline);
+/* replaces estimate_rates_and_branches(J, D, th, model) (:383-422). */
+double epv_estimate_rates_and_branches(uint64_t n_nodes, const double *J,
+                                       const double *D, double param_tol,
+                                       double *rates, double *branches, double *T,
+                                       double *baseline);
+/* replaces set_one_change_per_site_per_unit_time (:318-334). */
+void epv_set_one_change(double *rates, uint64_t n_nodes, double *branches);
+
+/* ---- instrumentation ------------------------------------------------------------- */
+/* Kernel launches issued by this context since creation (bench "gpu_launches"). */
+uint64_t epv_launch_count(const epv_ctx *ctx);
+/* Device time (ms, CUDA events on the context's stream) and launch count of the
+ * colour-pass kernel accumulated since the last call with reset != 0. */
+int epv_mh_kernel_time(epv_ctx *ctx, int reset, double *ms, uint64_t *launches);
+int epv_enable_kernel_timing(epv_ctx *ctx, int on);
+/* Total jumps currently stored, per node ([n_nodes], entry 0 zero). */
+int epv_jump_counts(epv_ctx *ctx, uint64_t *per_node);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
