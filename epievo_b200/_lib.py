@@ -1,0 +1,75 @@
+"""ctypes binding of libepievo_b200.so (the C-ABI in include/epievo_b200.h).
+
+There is no CPU fallback: if the library has not been built, or no CUDA device is
+usable, loading / context creation raises."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libepievo_b200.so")
+
+dp = C.POINTER(C.c_double)
+u64p = C.POINTER(C.c_uint64)
+u32p = C.POINTER(C.c_uint32)
+u8p = C.POINTER(C.c_uint8)
+ctx_p = C.c_void_p
+u64 = C.c_uint64
+
+# name -> (restype, argtypes); mirrors include/epievo_b200.h one to one
+SIGNATURES = {
+    "epv_create": (C.c_int, [C.POINTER(ctx_p), C.c_int]),
+    "epv_destroy": (None, [ctx_p]),
+    "epv_last_error": (C.c_char_p, [ctx_p]),
+    "epv_set_stream": (C.c_int, [ctx_p, C.c_void_p]),
+    "epv_synchronize": (C.c_int, [ctx_p]),
+    "epv_set_tree": (C.c_int, [ctx_p, u64, u64p, u64p, dp]),
+    "epv_set_model": (C.c_int, [ctx_p, dp, dp]),
+    "epv_set_shard": (C.c_int, [ctx_p, u64, u64, u64, u64, u64]),
+    "epv_upload_paths": (C.c_int, [ctx_p, u64, u64, u8p, u64p, dp, dp]),
+    "epv_paths_size": (C.c_int, [ctx_p, u64p, u64p, u64p]),
+    "epv_download_paths": (C.c_int, [ctx_p, u8p, u64p, dp, dp]),
+    "epv_reset": (C.c_int, [ctx_p]),
+    "epv_sweep": (C.c_int, [ctx_p, u64, u64, u64p]),
+    "epv_run_mcmc": (C.c_int, [ctx_p, u64, u64, u64, u64, dp, dp, dp]),
+    "epv_run_mcmc_raw": (C.c_int, [ctx_p, u64, u64, u64, u64, dp, dp, u64p]),
+    "epv_suffstats": (C.c_int, [ctx_p, dp, dp]),
+    "epv_llh_grad": (C.c_int, [ctx_p, dp, dp, dp]),
+    "epv_scale_jump_times": (C.c_int, [ctx_p, dp]),
+    "epv_pass": (C.c_int, [ctx_p, C.c_int, u64, u64]),
+    "epv_accept_count": (C.c_int, [ctx_p, C.c_int, u64p]),
+    "epv_site_debug": (C.c_int, [ctx_p, u64, u64, u64p, u64p, dp, dp, u64p, u64p, dp, dp, dp,
+                                 dp, dp]),
+    "epv_get_tri_llh": (C.c_int, [ctx_p, dp]),
+    "epv_end_cond_sample": (C.c_int, [ctx_p, C.c_double, C.c_double, C.c_int, C.c_int,
+                                      C.c_double, u64, u64, u64, u32p, dp]),
+    "epv_model_from_params": (None, [C.c_double] * 4 + [C.c_int] + [dp] * 4),
+    "epv_model_rebuild": (None, [dp] * 4),
+    "epv_rate_scaling_factor": (C.c_double, [dp]),
+    "epv_estimate_rates": (C.c_double, [u64, dp, dp, C.c_double, dp, dp, dp]),
+    "epv_estimate_rates_and_branches": (C.c_double, [u64, dp, dp, C.c_double, dp, dp, dp, dp]),
+    "epv_set_one_change": (None, [dp, u64, dp]),
+    "epv_launch_count": (u64, [ctx_p]),
+    "epv_mh_kernel_time": (C.c_int, [ctx_p, C.c_int, dp, u64p]),
+    "epv_enable_kernel_timing": (C.c_int, [ctx_p, C.c_int]),
+    "epv_jump_counts": (C.c_int, [ctx_p, u64p]),
+}
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                "epievo_b200: %s is missing -- build it with `python -m epievo_b200.build` "
+                "(or __graft_entry__.build()); there is no CPU fallback" % LIB_PATH)
+        lib = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib

@@ -1,0 +1,196 @@
+// api_paths.cu -- host exchange format <-> device CSR, capacity management.
+#include <algorithm>
+#include <cstring>
+
+#include "../../include/epievo_b200.h"
+#include "context.h"
+
+using namespace epv;
+
+namespace epv {
+
+// Current jump count of every branch, read from the tail of the offset arrays.
+int read_branch_totals(epv_ctx *c, std::vector<uint64_t> &tot) {
+  const int n_br = c->n_nodes - 1;
+  tot.assign(n_br, 0);
+  for (int bi = 0; bi < n_br; ++bi)
+    EPV_CUDA(c, cudaMemcpyAsync(reinterpret_cast<uint32_t *>(c->h_mail) + bi,
+                                c->d_off[c->cur] + (uint64_t)bi*c->off_pitch + c->n_sites,
+                                sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+  EPV_CUDA(c, cudaStreamSynchronize(c->stream));
+  for (int bi = 0; bi < n_br; ++bi) tot[bi] = reinterpret_cast<uint32_t *>(c->h_mail)[bi];
+  return 0;
+}
+
+static uint64_t capacity_for(uint64_t count, uint64_t n_sites) {
+  // room for the stationary fluctuation of the total plus growth between checks
+  uint64_t cap = count + count/2 + n_sites/16 + 4096;
+  return (cap + 15) & ~15ull;
+}
+
+// Allocate both jump buffers for the given per-branch capacities.
+static int alloc_jumps(epv_ctx *c, const std::vector<uint64_t> &cap, double *out[2],
+                       std::vector<uint64_t> &base, uint64_t &total) {
+  base.assign(cap.size(), 0);
+  total = 0;
+  for (size_t bi = 0; bi < cap.size(); ++bi) { base[bi] = total; total += cap[bi]; }
+  for (int k = 0; k < 2; ++k) {
+    out[k] = nullptr;
+    EPV_CUDA(c, cudaMalloc(&out[k], std::max<uint64_t>(total, 1)*sizeof(double)));
+  }
+  return 0;
+}
+
+// Grow any branch whose fill exceeds 3/4 of its capacity (called between sweeps).
+int maybe_regrow(epv_ctx *c, const std::vector<uint64_t> &tot) {
+  const int n_br = c->n_nodes - 1;
+  bool need = false;
+  for (int bi = 0; bi < n_br; ++bi)
+    if (tot[bi] > 0xfffffff0ull) return fail(c, "a branch holds more than 2^32 jumps on one GPU; use more shards");
+    else if (4*tot[bi] > 3*c->h_jcap[bi]) need = true;
+  if (!need) return 0;
+  std::vector<uint64_t> cap(n_br), base;
+  for (int bi = 0; bi < n_br; ++bi) cap[bi] = std::max(c->h_jcap[bi], capacity_for(2*tot[bi], c->n_sites));
+  double *nj[2]; uint64_t total;
+  if (int r = alloc_jumps(c, cap, nj, base, total)) return r;
+  for (int bi = 0; bi < n_br; ++bi)
+    EPV_CUDA(c, cudaMemcpyAsync(nj[c->cur] + base[bi], c->d_jmp[c->cur] + c->h_jbase[bi],
+                                tot[bi]*sizeof(double), cudaMemcpyDeviceToDevice, c->stream));
+  EPV_CUDA(c, cudaMemcpyAsync(c->d_jbase, base.data(), n_br*sizeof(uint64_t), cudaMemcpyHostToDevice, c->stream));
+  EPV_CUDA(c, cudaMemcpyAsync(c->d_jcap, cap.data(), n_br*sizeof(uint64_t), cudaMemcpyHostToDevice, c->stream));
+  EPV_CUDA(c, cudaStreamSynchronize(c->stream));
+  cudaFree(c->d_jmp[0]); cudaFree(c->d_jmp[1]);
+  c->d_jmp[0] = nj[0]; c->d_jmp[1] = nj[1];
+  c->h_jbase = base; c->h_jcap = cap; c->jmp_total_cap = total;
+  return 0;
+}
+
+}  // namespace epv
+
+extern "C" {
+
+int epv_upload_paths(epv_ctx *c, uint64_t n_sites, uint64_t n_nodes, const uint8_t *init_state,
+                     const uint64_t *row_off, const double *jumps, const double *tot_time) {
+  if (!c) return 1;
+  if (!c->n_nodes) return fail(c, "epv_set_tree must be called before epv_upload_paths");
+  if ((int)n_nodes != c->n_nodes) return fail(c, "paths and tree disagree on the number of nodes");
+  if (n_sites < 3) return fail(c, "need at least 3 sites");
+  cudaSetDevice(c->device);
+  if (!c->have_shard) {
+    c->n_global = n_sites; c->site_begin = 0; c->site_end = n_sites; c->halo_lo = c->halo_hi = 0;
+  }
+  if (n_sites != c->site_end - c->site_begin + c->halo_lo + c->halo_hi)
+    return fail(c, "n_sites does not match the shard set with epv_set_shard");
+  const int n_br = c->n_nodes - 1;
+  for (int b = 1; b < c->n_nodes; ++b)
+    if (tot_time[b] != c->h_branch[b])
+      return fail(c, "paths' tot_time differs from the tree's branch length (the reference "
+                     "asserts equality, Segment.cpp:76); rescale the paths or the tree");
+  EPV_CUDA(c, cudaStreamSynchronize(c->stream));
+  free_paths(c);
+
+  std::vector<uint64_t> count(n_br), cap(n_br);
+  if (row_off[0] != 0 || row_off[n_sites] != row_off[0]) return fail(c, "root rows must be empty");
+  for (int bi = 0; bi < n_br; ++bi) {
+    const uint64_t a = row_off[(uint64_t)(bi + 1)*n_sites], b = row_off[(uint64_t)(bi + 2)*n_sites];
+    if (b < a) return fail(c, "row_off must be non-decreasing");
+    count[bi] = b - a;
+    if (count[bi] > 0xfffffff0ull) return fail(c, "a branch holds more than 2^32 jumps on one GPU; use more shards");
+    cap[bi] = capacity_for(count[bi], n_sites);
+  }
+  c->n_sites = n_sites;
+  c->W = (c->n_nodes + 7)/8;
+  c->off_pitch = (n_sites + 1 + 31) & ~31ull;
+  c->n_tiles = (uint32_t)(((n_sites + 2)/3 + MH_THREADS - 1)/MH_THREADS);
+  if (int r = alloc_jumps(c, cap, c->d_jmp, c->h_jbase, c->jmp_total_cap)) return r;
+  c->h_jcap = cap;
+  for (int k = 0; k < 2; ++k)
+    EPV_CUDA(c, cudaMalloc(&c->d_off[k], (size_t)n_br*c->off_pitch*sizeof(uint32_t)));
+  EPV_CUDA(c, cudaMalloc(&c->d_jbase, n_br*sizeof(uint64_t)));
+  EPV_CUDA(c, cudaMalloc(&c->d_jcap, n_br*sizeof(uint64_t)));
+  EPV_CUDA(c, cudaMalloc(&c->d_state, (size_t)n_sites*c->W));
+  EPV_CUDA(c, cudaMalloc(&c->d_tri, n_sites*sizeof(double)));
+  EPV_CUDA(c, cudaMalloc(&c->d_desc, (size_t)n_br*c->n_tiles*sizeof(unsigned long long)));
+  EPV_CUDA(c, cudaMemsetAsync(c->d_desc, 0, (size_t)n_br*c->n_tiles*sizeof(unsigned long long), c->stream));
+  c->epoch = 0; c->cur = 0;
+  EPV_CUDA(c, cudaMemcpyAsync(c->d_jbase, c->h_jbase.data(), n_br*sizeof(uint64_t), cudaMemcpyHostToDevice, c->stream));
+  EPV_CUDA(c, cudaMemcpyAsync(c->d_jcap, c->h_jcap.data(), n_br*sizeof(uint64_t), cudaMemcpyHostToDevice, c->stream));
+
+  // raw host arrays -> device staging -> layout conversion on the device
+  uint8_t *t_init = nullptr; unsigned long long *t_off = nullptr;
+  const uint64_t n_rows = n_nodes*n_sites;
+  EPV_CUDA(c, cudaMalloc(&t_init, n_rows));
+  EPV_CUDA(c, cudaMalloc(&t_off, (n_rows + 1)*sizeof(unsigned long long)));
+  EPV_CUDA(c, cudaMemcpyAsync(t_init, init_state, n_rows, cudaMemcpyHostToDevice, c->stream));
+  EPV_CUDA(c, cudaMemcpyAsync(t_off, row_off, (n_rows + 1)*sizeof(unsigned long long), cudaMemcpyHostToDevice, c->stream));
+  launch_import(t_init, t_off, n_sites, c->n_nodes, c->d_off[0], c->off_pitch, c->d_state, c->W, c->stream);
+  ++c->launches;
+  for (int bi = 0; bi < n_br; ++bi)
+    if (count[bi])
+      EPV_CUDA(c, cudaMemcpyAsync(c->d_jmp[0] + c->h_jbase[bi], jumps + row_off[(uint64_t)(bi + 1)*n_sites],
+                                  count[bi]*sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  EPV_CUDA(c, cudaStreamSynchronize(c->stream));
+  cudaFree(t_init); cudaFree(t_off);
+  EPV_CUDA(c, cudaGetLastError());
+  return 0;
+}
+
+int epv_paths_size(epv_ctx *c, uint64_t *n_sites, uint64_t *n_nodes, uint64_t *n_jumps) {
+  if (!c) return 1;
+  if (!c->n_sites) return fail(c, "no paths loaded");
+  cudaSetDevice(c->device);
+  std::vector<uint64_t> tot;
+  if (int r = read_branch_totals(c, tot)) return r;
+  uint64_t s = 0;
+  for (uint64_t t : tot) s += t;
+  if (n_sites) *n_sites = c->n_sites;
+  if (n_nodes) *n_nodes = (uint64_t)c->n_nodes;
+  if (n_jumps) *n_jumps = s;
+  return 0;
+}
+
+int epv_jump_counts(epv_ctx *c, uint64_t *per_node) {
+  if (!c) return 1;
+  if (!c->n_sites) return fail(c, "no paths loaded");
+  cudaSetDevice(c->device);
+  std::vector<uint64_t> tot;
+  if (int r = read_branch_totals(c, tot)) return r;
+  per_node[0] = 0;
+  for (int bi = 0; bi + 1 < c->n_nodes; ++bi) per_node[bi + 1] = tot[bi];
+  return 0;
+}
+
+int epv_download_paths(epv_ctx *c, uint8_t *init_state, uint64_t *row_off, double *jumps,
+                       double *tot_time) {
+  if (!c) return 1;
+  if (!c->n_sites) return fail(c, "no paths loaded");
+  cudaSetDevice(c->device);
+  if (int r = check_device_flags(c)) return r;
+  const int n_br = c->n_nodes - 1;
+  std::vector<uint64_t> tot;
+  if (int r = read_branch_totals(c, tot)) return r;
+  std::vector<uint64_t> prefix(n_br + 1, 0);
+  for (int bi = 0; bi < n_br; ++bi) prefix[bi + 1] = prefix[bi] + tot[bi];
+  const uint64_t n_rows = (uint64_t)c->n_nodes*c->n_sites;
+  uint8_t *t_init = nullptr; unsigned long long *t_off = nullptr; uint64_t *t_pre = nullptr;
+  EPV_CUDA(c, cudaMalloc(&t_init, n_rows));
+  EPV_CUDA(c, cudaMalloc(&t_off, (n_rows + 1)*sizeof(unsigned long long)));
+  EPV_CUDA(c, cudaMalloc(&t_pre, (n_br + 1)*sizeof(uint64_t)));
+  EPV_CUDA(c, cudaMemcpyAsync(t_pre, prefix.data(), (n_br + 1)*sizeof(uint64_t), cudaMemcpyHostToDevice, c->stream));
+  launch_export(c->d_off[c->cur], c->off_pitch, c->d_state, c->W, c->n_sites, c->n_nodes, t_pre,
+                t_init, t_off, c->stream);
+  ++c->launches;
+  EPV_CUDA(c, cudaMemcpyAsync(init_state, t_init, n_rows, cudaMemcpyDeviceToHost, c->stream));
+  EPV_CUDA(c, cudaMemcpyAsync(row_off, t_off, (n_rows + 1)*sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+  for (int bi = 0; bi < n_br; ++bi)
+    if (tot[bi])
+      EPV_CUDA(c, cudaMemcpyAsync(jumps + prefix[bi], c->d_jmp[c->cur] + c->h_jbase[bi],
+                                  tot[bi]*sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  EPV_CUDA(c, cudaStreamSynchronize(c->stream));
+  cudaFree(t_init); cudaFree(t_off); cudaFree(t_pre);
+  for (int b = 0; b < c->n_nodes; ++b) tot_time[b] = c->h_branch[b];
+  EPV_CUDA(c, cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,258 @@
+// api_sampler.cu -- reset / sweep / run_mcmc / sufficient statistics / rescale.
+#include <cstring>
+
+#include "../../include/epievo_b200.h"
+#include "context.h"
+
+using namespace epv;
+
+namespace epv {
+int read_branch_totals(epv_ctx *c, std::vector<uint64_t> &tot);
+int maybe_regrow(epv_ctx *c, const std::vector<uint64_t> &tot);
+}
+
+namespace {
+
+int ready(epv_ctx *c) {
+  if (!c) return 1;
+  if (!c->n_sites) return fail(c, "no paths loaded");
+  if (!c->have_model) return fail(c, "epv_set_model has not been called");
+  cudaSetDevice(c->device);
+  return 0;
+}
+
+// Owned sites that have both neighbours globally: the J/D and tri_llh range.
+void interior(const epv_ctx *c, uint64_t &lo, uint64_t &hi) {
+  lo = c->upd_lo(); hi = c->upd_hi();
+  const int64_t g0 = c->global0();
+  if (g0 + (int64_t)lo < 1) lo = (uint64_t)(1 - g0);
+  if (g0 + (int64_t)hi > (int64_t)c->n_global - 1) hi = (uint64_t)((int64_t)c->n_global - 1 - g0);
+}
+
+int do_reset(epv_ctx *c) {
+  launch_tri_llh(c->mp, c->view(c->cur), c->d_state, c->W, c->tree(), c->n_sites, c->d_tri, c->stream);
+  ++c->launches;
+  c->tri_valid = true;
+  return 0;
+}
+
+int one_pass(epv_ctx *c, int colour, uint64_t seed, uint32_t sweep) {
+  if (++c->epoch >= (1u << 30)) {
+    EPV_CUDA(c, cudaMemsetAsync(c->d_desc, 0, (size_t)(c->n_nodes - 1)*c->n_tiles*sizeof(unsigned long long), c->stream));
+    c->epoch = 1;
+  }
+  PassArgs a;
+  a.mp = c->mp;
+  a.in = c->view(c->cur);
+  a.off_out = c->d_off[c->cur ^ 1]; a.jmp_out = c->d_jmp[c->cur ^ 1];
+  a.jcap = c->d_jcap;
+  a.state = c->d_state; a.W = c->W; a.tree = c->tree(); a.tri_llh = c->d_tri;
+  a.n_sites = c->n_sites; a.upd_lo = c->upd_lo(); a.upd_hi = c->upd_hi();
+  a.global0 = c->global0(); a.n_global = c->n_global;
+  a.colour = colour; a.seed = seed; a.sweep = sweep;
+  a.desc = c->d_desc; a.n_tiles = c->n_tiles; a.epoch = c->epoch;
+  a.ticket = c->d_ticket; a.ticket_base = c->ticket_base;
+  a.scratch = c->d_scratch; a.scratch_ctr = c->d_scratch_ctr;
+  a.scratch_slots = c->scratch_slots; a.scratch_cap = c->scratch_cap;
+  a.err = c->d_err; a.n_accept = c->d_nacc;
+  EPV_CUDA(c, cudaMemsetAsync(c->d_scratch_ctr, 0, sizeof(uint32_t), c->stream));
+  if (c->timing) cudaEventRecord(c->ev0, c->stream);
+  launch_mh_pass(a, c->stream);
+  if (c->timing) {
+    cudaEventRecord(c->ev1, c->stream);
+    cudaEventSynchronize(c->ev1);
+    float ms = 0.f; cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+    c->mh_ms += ms;
+  }
+  ++c->launches; ++c->mh_launches;
+  c->ticket_base += c->n_tiles;
+  c->cur ^= 1;
+  c->stats_valid = false;
+  return 0;
+}
+
+// One sweep = three colour passes.  Single-GPU shards need no exchange in between.
+int one_sweep(epv_ctx *c, uint64_t seed, uint64_t sweep_idx) {
+  for (int colour = 0; colour < 3; ++colour)
+    if (int r = one_pass(c, colour, seed, (uint32_t)sweep_idx)) return r;
+  return 0;
+}
+
+// After a sweep: surface device-side failures and keep capacity headroom.
+int housekeeping(epv_ctx *c) {
+  if (int r = check_device_flags(c)) return r;
+  std::vector<uint64_t> tot;
+  if (int r = read_branch_totals(c, tot)) return r;
+  return maybe_regrow(c, tot);
+}
+
+int read_accepts(epv_ctx *c, uint64_t *n) {
+  EPV_CUDA(c, cudaMemcpyAsync(c->h_mail, c->d_nacc, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+  EPV_CUDA(c, cudaStreamSynchronize(c->stream));
+  *n = c->h_mail[0];
+  return 0;
+}
+
+int do_suffstats(epv_ctx *c) {
+  uint64_t lo, hi; interior(c, lo, hi);
+  launch_suffstats(c->view(c->cur), c->d_state, c->W, c->tree(), c->n_sites, lo, hi, c->d_J, c->d_D,
+                   c->d_ss, c->stream, c->sm_count);
+  c->launches += 2;
+  c->stats_valid = true;
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int epv_reset(epv_ctx *c) {
+  if (int r = ready(c)) return r;
+  if (int r = do_reset(c)) return r;
+  EPV_CUDA(c, cudaGetLastError());
+  return 0;
+}
+
+int epv_sweep(epv_ctx *c, uint64_t seed, uint64_t sweep_idx, uint64_t *n_accepted) {
+  if (int r = ready(c)) return r;
+  if (!c->tri_valid) if (int r = do_reset(c)) return r;
+  EPV_CUDA(c, cudaMemsetAsync(c->d_nacc, 0, sizeof(unsigned long long), c->stream));
+  if (int r = one_sweep(c, seed, sweep_idx)) return r;
+  if (int r = housekeeping(c)) return r;
+  uint64_t n = 0;
+  if (int r = read_accepts(c, &n)) return r;
+  if (n_accepted) *n_accepted = n;
+  EPV_CUDA(c, cudaGetLastError());
+  return 0;
+}
+
+int epv_run_mcmc_raw(epv_ctx *c, uint64_t burn_in, uint64_t batch, uint64_t seed,
+                     uint64_t first_sweep, double *J_sum, double *D_sum, uint64_t *n_accepted) {
+  if (int r = ready(c)) return r;
+  if (c->have_shard && (c->halo_lo || c->halo_hi))
+    return fail(c, "epv_run_mcmc needs a halo exchange between colour passes on a sharded "
+                   "context; drive epv_pass/epv_halo_* from the multi-GPU host loop instead");
+  if (!c->tri_valid) if (int r = do_reset(c)) return r;
+  const size_t nb = (size_t)c->n_nodes*8*sizeof(double);
+  uint64_t sweep = first_sweep;
+  for (uint64_t i = 0; i < burn_in; ++i, ++sweep) {          // SingleSiteSampler.cpp:560-561
+    if (int r = one_sweep(c, seed, sweep)) return r;
+    if (int r = housekeeping(c)) return r;
+  }
+  EPV_CUDA(c, cudaMemsetAsync(c->d_nacc, 0, sizeof(unsigned long long), c->stream));
+  EPV_CUDA(c, cudaMemsetAsync(c->d_Jsum, 0, nb, c->stream));
+  EPV_CUDA(c, cudaMemsetAsync(c->d_Dsum, 0, nb, c->stream));
+  for (uint64_t i = 0; i < batch; ++i, ++sweep) {            // :576-587
+    if (int r = one_sweep(c, seed, sweep)) return r;
+    if (int r = housekeeping(c)) return r;
+    if (int r = do_suffstats(c)) return r;
+    launch_axpy_stats(c->d_Jsum, c->d_Dsum, c->d_J, c->d_D, c->n_nodes*8, c->stream);
+    ++c->launches;
+  }
+  EPV_CUDA(c, cudaMemcpyAsync(J_sum, c->d_Jsum, nb, cudaMemcpyDeviceToHost, c->stream));
+  EPV_CUDA(c, cudaMemcpyAsync(D_sum, c->d_Dsum, nb, cudaMemcpyDeviceToHost, c->stream));
+  uint64_t n = 0;
+  if (int r = read_accepts(c, &n)) return r;
+  if (n_accepted) *n_accepted = n;
+  EPV_CUDA(c, cudaGetLastError());
+  return 0;
+}
+
+int epv_run_mcmc(epv_ctx *c, uint64_t burn_in, uint64_t batch, uint64_t seed,
+                 uint64_t first_sweep, double *J, double *D, double *acc_rate) {
+  uint64_t n = 0;
+  if (int r = epv_run_mcmc_raw(c, burn_in, batch, seed, first_sweep, J, D, &n)) return r;
+  for (int i = 0; i < c->n_nodes*8; ++i) {                   // batch average, :590-594
+    J[i] /= batch; D[i] /= batch;
+  }
+  if (acc_rate) *acc_rate = (double)n/(batch*(c->n_global - 2));   // :597
+  return 0;
+}
+
+int epv_suffstats(epv_ctx *c, double *J, double *D) {
+  if (!c) return 1;
+  if (!c->n_sites) return fail(c, "no paths loaded");
+  cudaSetDevice(c->device);
+  if (int r = do_suffstats(c)) return r;
+  const size_t nb = (size_t)c->n_nodes*8*sizeof(double);
+  EPV_CUDA(c, cudaMemcpyAsync(J, c->d_J, nb, cudaMemcpyDeviceToHost, c->stream));
+  EPV_CUDA(c, cudaMemcpyAsync(D, c->d_D, nb, cudaMemcpyDeviceToHost, c->stream));
+  EPV_CUDA(c, cudaStreamSynchronize(c->stream));
+  EPV_CUDA(c, cudaGetLastError());
+  return 0;
+}
+
+int epv_llh_grad(epv_ctx *c, const double *rates, double *llh, double *grad) {
+  if (!c) return 1;
+  if (!c->stats_valid) return fail(c, "epv_llh_grad needs a preceding epv_suffstats on the current paths");
+  cudaSetDevice(c->device);
+  launch_llh_grad(c->d_J, c->d_D, c->n_nodes, rates, c->d_out9, c->stream);
+  ++c->launches;
+  double out[9];
+  EPV_CUDA(c, cudaMemcpyAsync(c->h_mail, c->d_out9, sizeof out, cudaMemcpyDeviceToHost, c->stream));
+  EPV_CUDA(c, cudaStreamSynchronize(c->stream));
+  std::memcpy(out, c->h_mail, sizeof out);
+  *llh = out[0];
+  for (int i = 0; i < 8; ++i) grad[i] = out[1 + i];
+  return 0;
+}
+
+int epv_scale_jump_times(epv_ctx *c, const double *new_branches) {
+  if (!c) return 1;
+  if (!c->n_sites) return fail(c, "no paths loaded");
+  cudaSetDevice(c->device);
+  std::vector<double> scale(c->n_nodes, 1.0);
+  for (int b = 1; b < c->n_nodes; ++b) {
+    if (!(new_branches[b] > 0.0)) return fail(c, "branch lengths must be positive");
+    scale[b] = new_branches[b]/c->h_branch[b];                // ParamEstimation.cpp:373
+  }
+  double *d_scale = reinterpret_cast<double *>(c->d_mail);
+  EPV_CUDA(c, cudaMemcpyAsync(d_scale, scale.data(), c->n_nodes*sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  launch_scale_jumps(c->d_jmp[c->cur], c->d_jbase, c->d_off[c->cur], c->off_pitch, c->n_sites,
+                     c->n_nodes - 1, d_scale, c->stream);
+  ++c->launches;
+  for (int b = 1; b < c->n_nodes; ++b) c->h_branch[b] = new_branches[b];
+  EPV_CUDA(c, cudaMemcpyAsync(c->d_branch, c->h_branch.data(), c->n_nodes*sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  EPV_CUDA(c, cudaStreamSynchronize(c->stream));
+  c->tri_valid = false; c->stats_valid = false;
+  EPV_CUDA(c, cudaGetLastError());
+  return 0;
+}
+
+uint64_t epv_launch_count(const epv_ctx *c) { return c ? c->launches : 0; }
+
+int epv_enable_kernel_timing(epv_ctx *c, int on) { if (!c) return 1; c->timing = on != 0; return 0; }
+
+int epv_mh_kernel_time(epv_ctx *c, int reset, double *ms, uint64_t *launches) {
+  if (!c) return 1;
+  if (ms) *ms = c->mh_ms;
+  if (launches) *launches = c->mh_launches;
+  if (reset) { c->mh_ms = 0.0; c->mh_launches = 0; }
+  return 0;
+}
+
+}  // extern "C"
+
+extern "C" {
+
+int epv_pass(epv_ctx *c, int colour, uint64_t seed, uint64_t sweep_idx) {
+  if (int r = ready(c)) return r;
+  if (colour < 0 || colour > 2) return fail(c, "colour must be 0, 1 or 2");
+  if (!c->tri_valid) if (int r = do_reset(c)) return r;
+  if (int r = one_pass(c, colour, seed, (uint32_t)sweep_idx)) return r;
+  if (colour == 2) if (int r = housekeeping(c)) return r;
+  EPV_CUDA(c, cudaGetLastError());
+  return 0;
+}
+
+int epv_accept_count(epv_ctx *c, int reset, uint64_t *n_accepted) {
+  if (!c) return 1;
+  cudaSetDevice(c->device);
+  uint64_t n = 0;
+  if (int r = read_accepts(c, &n)) return r;
+  if (n_accepted) *n_accepted = n;
+  if (reset) EPV_CUDA(c, cudaMemsetAsync(c->d_nacc, 0, sizeof(unsigned long long), c->stream));
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,86 @@
+// context.h -- the opaque epv_ctx behind the C-ABI (internal).
+#pragma once
+#include <string>
+#include <vector>
+
+#include "kernels.h"
+
+struct epv_ctx {
+  int device = 0, sm_count = 148;
+  cudaStream_t own_stream = nullptr, stream = nullptr;
+  std::string error;
+
+  // tree
+  int n_nodes = 0;
+  std::vector<int> h_parent, h_subtree;
+  std::vector<double> h_branch;
+  int *d_parent = nullptr, *d_subtree = nullptr;
+  double *d_branch = nullptr;
+  // model
+  bool have_model = false;
+  epv::ModelParams mp;
+  // shard
+  bool have_shard = false;
+  uint64_t n_global = 0, site_begin = 0, site_end = 0, halo_lo = 0, halo_hi = 0;
+
+  // paths
+  uint64_t n_sites = 0, off_pitch = 0;
+  int W = 0;
+  uint32_t *d_off[2] = {nullptr, nullptr};
+  double *d_jmp[2] = {nullptr, nullptr};
+  uint64_t *d_jbase = nullptr, *d_jcap = nullptr;
+  std::vector<uint64_t> h_jbase, h_jcap;
+  uint64_t jmp_total_cap = 0;
+  int cur = 0;
+  uint8_t *d_state = nullptr;
+  double *d_tri = nullptr;
+  bool tri_valid = false;
+
+  // colour-pass machinery
+  unsigned long long *d_desc = nullptr;
+  uint32_t n_tiles = 0, epoch = 0, ticket_base = 0;
+  uint32_t *d_ticket = nullptr, *d_scratch_ctr = nullptr;
+  double *d_scratch = nullptr;
+  uint32_t scratch_slots = 2048, scratch_cap = 2048;
+  unsigned *d_err = nullptr;
+  unsigned long long *d_nacc = nullptr;
+
+  // statistics
+  double *d_J = nullptr, *d_D = nullptr, *d_Jsum = nullptr, *d_Dsum = nullptr, *d_out9 = nullptr;
+  unsigned long long *d_ss = nullptr;
+  bool stats_valid = false;
+
+  // small pinned host mailbox
+  unsigned long long *h_mail = nullptr;      // [64 + n_nodes]
+  unsigned long long *d_mail = nullptr;
+
+  // halo blobs
+  void *d_halo[4] = {nullptr, nullptr, nullptr, nullptr};
+  uint64_t halo_bytes[4] = {0, 0, 0, 0};
+
+  // instrumentation
+  uint64_t launches = 0, mh_launches = 0;
+  bool timing = false;
+  double mh_ms = 0.0;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+
+  epv::PathView view(int which) const {
+    epv::PathView v; v.off = d_off[which]; v.jmp = d_jmp[which]; v.jbase = d_jbase;
+    v.off_pitch = off_pitch; return v;
+  }
+  epv::TreeDev tree() const {
+    epv::TreeDev t; t.n_nodes = n_nodes; t.parent = d_parent; t.subtree = d_subtree;
+    t.branch = d_branch; return t;
+  }
+  uint64_t upd_lo() const { return halo_lo; }
+  uint64_t upd_hi() const { return n_sites - halo_hi; }
+  int64_t global0() const { return (int64_t)site_begin - (int64_t)halo_lo; }
+};
+
+namespace epv {
+int fail(epv_ctx *c, const std::string &msg);
+int check_cuda(epv_ctx *c, cudaError_t e, const char *what);
+void free_paths(epv_ctx *c);
+int check_device_flags(epv_ctx *c);   // reads d_err, turns sticky flags into an error
+}
+#define EPV_CUDA(c, call) do { if (int _r = epv::check_cuda((c), (call), #call)) return _r; } while (0)

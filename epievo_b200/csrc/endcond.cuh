@@ -24,7 +24,7 @@ trunc_exp(double r, double one_minus_e, double U) {
 // Appends the sampled jump times (offset by t_off) to out[n..cap).  Returns the new
 // count, or -1 if cap was exceeded (the caller restarts with a larger buffer), or -2
 // if the iteration cap was hit.
-__device__ __noinline__ int
+static __device__ __noinline__ int
 end_cond_sample(double rate0, double rate1, int start, int end, double T,
                 double t_off, Philox &rng, double *out, int n, int cap) {
   const double s = rate0 + rate1;

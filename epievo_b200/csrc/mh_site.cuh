@@ -77,7 +77,7 @@ branch_next_vectors(const ModelParams &mp, const Row &L, const Row &R, double to
 }
 
 // "next" vector of interval i >= PBUF, recomputed from q (rare: > PBUF intervals).
-__device__ __noinline__ void
+static __device__ __noinline__ void
 next_vector_slow(const ModelParams &mp, const Row &L, const Row &R, double tot,
                  double q0, double q1, int i, double &n0, double &n1) {
   const int n_int = L.n + R.n + 1;

@@ -1,0 +1,205 @@
+"""Thin object wrapper over the C-ABI context (one context = one GPU)."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Tuple
+
+import numpy as np
+
+from . import _lib as L
+from .paths import PathSet, Tree
+
+
+def _d(a):
+    return a.ctypes.data_as(L.dp)
+
+
+def _u64(a):
+    return a.ctypes.data_as(L.u64p)
+
+
+def _u8(a):
+    return a.ctypes.data_as(L.u8p)
+
+
+def _f64(x) -> np.ndarray:
+    return np.ascontiguousarray(x, dtype=np.float64)
+
+
+class EpvError(RuntimeError):
+    pass
+
+
+class Context:
+    def __init__(self, device: int = 0):
+        self.lib = L.load()
+        self.h = L.ctx_p()
+        if self.lib.epv_create(C.byref(self.h), device) != 0:
+            self.h = None
+            raise EpvError("epv_create failed: no usable CUDA device %d (no CPU fallback)" % device)
+        self.n_nodes = 0
+        self.n_sites = 0
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.epv_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc: int):
+        if rc != 0:
+            raise EpvError(self.lib.epv_last_error(self.h).decode())
+
+    # -- setup --------------------------------------------------------------------
+    def set_stream(self, cuda_stream_ptr: int):
+        self._ck(self.lib.epv_set_stream(self.h, C.c_void_p(cuda_stream_ptr)))
+
+    def synchronize(self):
+        self._ck(self.lib.epv_synchronize(self.h))
+
+    def set_tree(self, tree: Tree):
+        ss = np.ascontiguousarray(tree.subtree_sizes, np.uint64)
+        pi = np.ascontiguousarray(tree.parent_ids, np.uint64)
+        br = _f64(tree.branches)
+        self._ck(self.lib.epv_set_tree(self.h, tree.n_nodes, _u64(ss), _u64(pi), _d(br)))
+        self.n_nodes = tree.n_nodes
+
+    def set_model(self, rates, T):
+        self._ck(self.lib.epv_set_model(self.h, _d(_f64(rates)), _d(_f64(T))))
+
+    def set_shard(self, n_global, site_begin, site_end, halo_lo, halo_hi):
+        self._ck(self.lib.epv_set_shard(self.h, n_global, site_begin, site_end, halo_lo, halo_hi))
+
+    def upload_paths(self, ps: PathSet):
+        j = ps.jumps if len(ps.jumps) else np.zeros(1)
+        self._ck(self.lib.epv_upload_paths(self.h, ps.n_sites, ps.n_nodes, _u8(ps.init_state),
+                                           _u64(ps.row_off), _d(j), _d(ps.tot_time)))
+        self.n_sites = ps.n_sites
+
+    def upload_raw(self, n_sites, n_nodes, init_ptr, off_ptr, jumps_ptr, tot_time):
+        """Upload from raw host addresses (e.g. pinned torch tensors)."""
+        tt = _f64(tot_time)
+        self._ck(self.lib.epv_upload_paths(
+            self.h, n_sites, n_nodes, C.cast(init_ptr, L.u8p), C.cast(off_ptr, L.u64p),
+            C.cast(jumps_ptr, L.dp), _d(tt)))
+        self.n_sites = n_sites
+
+    def paths_size(self) -> Tuple[int, int, int]:
+        a, b, c = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        self._ck(self.lib.epv_paths_size(self.h, C.byref(a), C.byref(b), C.byref(c)))
+        return a.value, b.value, c.value
+
+    def download_paths(self, node_names=()) -> PathSet:
+        n_sites, n_nodes, n_jumps = self.paths_size()
+        init = np.zeros(n_sites * n_nodes, np.uint8)
+        off = np.zeros(n_sites * n_nodes + 1, np.uint64)
+        jumps = np.zeros(max(1, n_jumps))
+        tot = np.zeros(n_nodes)
+        self._ck(self.lib.epv_download_paths(self.h, _u8(init), _u64(off), _d(jumps), _d(tot)))
+        return PathSet(n_sites, n_nodes, init, off, jumps[:n_jumps].copy(), tot, list(node_names))
+
+    def download_raw(self, init_ptr, off_ptr, jumps_ptr):
+        tot = np.zeros(self.n_nodes)
+        self._ck(self.lib.epv_download_paths(
+            self.h, C.cast(init_ptr, L.u8p), C.cast(off_ptr, L.u64p), C.cast(jumps_ptr, L.dp),
+            _d(tot)))
+
+    def jump_counts(self) -> np.ndarray:
+        out = np.zeros(self.n_nodes, np.uint64)
+        self._ck(self.lib.epv_jump_counts(self.h, _u64(out)))
+        return out
+
+    # -- sampler ------------------------------------------------------------------
+    def reset(self):
+        self._ck(self.lib.epv_reset(self.h))
+
+    def sweep(self, seed: int, sweep_idx: int) -> int:
+        n = C.c_uint64()
+        self._ck(self.lib.epv_sweep(self.h, seed, sweep_idx, C.byref(n)))
+        return n.value
+
+    def colour_pass(self, colour: int, seed: int, sweep_idx: int):
+        self._ck(self.lib.epv_pass(self.h, colour, seed, sweep_idx))
+
+    def accept_count(self, reset: bool = True) -> int:
+        n = C.c_uint64()
+        self._ck(self.lib.epv_accept_count(self.h, int(reset), C.byref(n)))
+        return n.value
+
+    def run_mcmc(self, burn_in: int, batch: int, seed: int, first_sweep: int = 0):
+        J = np.zeros(self.n_nodes * 8)
+        D = np.zeros(self.n_nodes * 8)
+        acc = C.c_double()
+        self._ck(self.lib.epv_run_mcmc(self.h, burn_in, batch, seed, first_sweep, _d(J), _d(D),
+                                       C.byref(acc)))
+        return J.reshape(-1, 8), D.reshape(-1, 8), acc.value
+
+    def run_mcmc_raw(self, burn_in: int, batch: int, seed: int, first_sweep: int = 0):
+        J = np.zeros(self.n_nodes * 8)
+        D = np.zeros(self.n_nodes * 8)
+        n = C.c_uint64()
+        self._ck(self.lib.epv_run_mcmc_raw(self.h, burn_in, batch, seed, first_sweep, _d(J),
+                                           _d(D), C.byref(n)))
+        return J.reshape(-1, 8), D.reshape(-1, 8), n.value
+
+    # -- statistics -----------------------------------------------------------------
+    def suffstats(self):
+        J = np.zeros(self.n_nodes * 8)
+        D = np.zeros(self.n_nodes * 8)
+        self._ck(self.lib.epv_suffstats(self.h, _d(J), _d(D)))
+        return J.reshape(-1, 8), D.reshape(-1, 8)
+
+    def llh_grad(self, rates):
+        llh = C.c_double()
+        g = np.zeros(8)
+        self._ck(self.lib.epv_llh_grad(self.h, _d(_f64(rates)), C.byref(llh), _d(g)))
+        return llh.value, g
+
+    def scale_jump_times(self, new_branches):
+        self._ck(self.lib.epv_scale_jump_times(self.h, _d(_f64(new_branches))))
+
+    # -- parity probes ----------------------------------------------------------------
+    def site_debug(self, site: int, cap: int = 4096):
+        nn = self.n_nodes
+        k = C.c_uint64()
+        seg_off = np.zeros(nn + 1, np.uint64)
+        r0, r1, ln = np.zeros(cap), np.zeros(cap), np.zeros(cap)
+        t0, t1 = np.zeros(cap, np.uint64), np.zeros(cap, np.uint64)
+        p, q = np.zeros(2 * cap), np.zeros(2 * nn)
+        rp, lp = C.c_double(), C.c_double()
+        self._ck(self.lib.epv_site_debug(self.h, site, cap, C.byref(k), _u64(seg_off), _d(r0),
+                                         _d(r1), _u64(t0), _u64(t1), _d(ln), _d(p), _d(q),
+                                         C.byref(rp), C.byref(lp)))
+        n = k.value
+        return dict(seg_off=seg_off, rate0=r0[:n], rate1=r1[:n], trip0=t0[:n], trip1=t1[:n],
+                    len=ln[:n], p=p[:2 * n].reshape(-1, 2), q=q.reshape(-1, 2),
+                    root_p0=rp.value, proposal_logp=lp.value)
+
+    def tri_llh(self) -> np.ndarray:
+        out = np.zeros(self.n_sites)
+        self._ck(self.lib.epv_get_tri_llh(self.h, _d(out)))
+        return out
+
+    def end_cond_sample(self, r0, r1, a, b, T, seed, n, cap=32):
+        nj = np.zeros(n, np.uint32)
+        j = np.zeros(n * cap)
+        self._ck(self.lib.epv_end_cond_sample(self.h, r0, r1, a, b, T, seed, n, cap,
+                                              nj.ctypes.data_as(L.u32p), _d(j)))
+        return nj, j.reshape(n, cap)
+
+    # -- instrumentation ----------------------------------------------------------------
+    def launch_count(self) -> int:
+        return int(self.lib.epv_launch_count(self.h))
+
+    def enable_kernel_timing(self, on: bool):
+        self._ck(self.lib.epv_enable_kernel_timing(self.h, int(on)))
+
+    def mh_kernel_time(self, reset: bool = True):
+        ms, n = C.c_double(), C.c_uint64()
+        self._ck(self.lib.epv_mh_kernel_time(self.h, int(reset), C.byref(ms), C.byref(n)))
+        return ms.value, n.value

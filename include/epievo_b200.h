@@ -110,16 +110,12 @@ int epv_llh_grad(epv_ctx *ctx, const double *rates, double *llh, double *grad);
  * lengths become new_branches. */
 int epv_scale_jump_times(epv_ctx *ctx, const double *new_branches);
 
-/* ---- halo exchange (multi-GPU; see epv_set_shard) -------------------------------- */
-/* Pack the paths of `count` sites starting at local site `first` into a
- * self-describing blob in DEVICE memory owned by the context; returns its address
- * and size.  The peer feeds the blob to epv_halo_unpack, which overwrites its own
- * `count` sites starting at local site `first`.  Blobs never pass through the host. */
-int epv_halo_pack(epv_ctx *ctx, uint64_t first, uint64_t count, int slot,
-                  void **dev_blob, uint64_t *n_bytes);
-int epv_halo_recv_buffer(epv_ctx *ctx, int slot, uint64_t n_bytes, void **dev_blob);
-int epv_halo_unpack(epv_ctx *ctx, uint64_t first, uint64_t count, int slot);
-uint64_t epv_halo_blob_bytes(const epv_ctx *ctx, uint64_t count);
+/* ---- multi-GPU building blocks (see epv_set_shard) --------------------------------- */
+/* One stride-3 colour pass (colour 0,1,2) of sweep sweep_idx over this shard's sites;
+ * epv_sweep is three of these.  A sharded driver exchanges halos between passes. */
+int epv_pass(epv_ctx *ctx, int colour, uint64_t seed, uint64_t sweep_idx);
+/* Accept counter of the passes issued since the last call with reset != 0. */
+int epv_accept_count(epv_ctx *ctx, int reset, uint64_t *n_accepted);
 
 /* ---- deterministic per-site intermediates (parity tests of a2/a3/a4/a7) --------- */
 /* For local site `site`: the neighbour-interval lists of every node

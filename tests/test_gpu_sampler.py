@@ -1,0 +1,86 @@
+"""Structural checks of the Metropolis-Hastings sweep on the GPU: every invariant the
+reference's update preserves (SingleSiteSampler.cpp:482-536) must hold after sweeps,
+and the cached tri_llh must equal a from-scratch recomputation."""
+import numpy as np
+import pytest
+
+from epievo_b200.paths import Tree
+from synth import rel_close, synth_paths, ref_test_tree
+
+pytestmark = pytest.mark.gpu
+
+
+def check_valid(tree, before, after):
+    n = before.n_sites
+    assert (after.n_sites, after.n_nodes) == (n, before.n_nodes)
+    st0 = before.init_state.reshape(before.n_nodes, n)
+    st1 = after.init_state.reshape(after.n_nodes, n)
+    e0, e1 = before.end_state(), after.end_state()
+    for v in range(1, tree.n_nodes):
+        par = int(tree.parent_ids[v])
+        if par == 0:
+            assert np.array_equal(st1[v], st0[1])          # root state never resampled (:441)
+        else:
+            assert np.array_equal(st1[v][1:-1], e1[par][1:-1])   # branch starts at parent's end
+        if tree.is_leaf(v):
+            assert np.array_equal(e1[v], e0[v])            # leaf data preserved
+        T = float(tree.branches[v])
+        for s in range(n):
+            r = after.row(v, s)
+            if len(r):
+                assert r[0] > 0.0 and r[-1] < T and np.all(np.diff(r) > 0)
+    # boundary sites are never updated (:545)
+    for v in range(1, tree.n_nodes):
+        assert np.array_equal(after.row(v, 0), before.row(v, 0))
+        assert np.array_equal(after.row(v, n - 1), before.row(v, n - 1))
+
+
+@pytest.mark.parametrize("case", ["testtree", "pair", "bal8", "bal32"])
+def test_sweeps_preserve_invariants(ctx, cpu, model, case):
+    tree = {"testtree": ref_test_tree, "pair": lambda: Tree.pair(1.0),
+            "bal8": lambda: Tree.balanced(8, 0.05), "bal32": lambda: Tree.balanced(32, 0.05)}[case]()
+    n = 1000
+    ps = synth_paths(tree, n, 5, 1.0)
+    rates, T = model
+    ctx.set_tree(tree); ctx.set_model(rates, T); ctx.upload_paths(ps); ctx.reset()
+    acc = 0
+    for sw in range(4):
+        acc += ctx.sweep(1234, sw)
+    assert 0.5*4*(n - 2) < acc <= 4*(n - 2)
+    out = ctx.download_paths()
+    check_valid(tree, ps, out)
+    assert not out.same_as(ps)
+    cached = ctx.tri_llh()
+    cpu.load_paths(out)
+    assert rel_close(cached, cpu.tri_llh(rates, T), 1e-9, atol=1e-12)
+    # determinism: same seed, same result
+    ctx.upload_paths(ps); ctx.reset()
+    for sw in range(4):
+        ctx.sweep(1234, sw)
+    assert ctx.download_paths().same_as(out)
+
+
+def test_end_cond_sampler_matches_analytic_expectations(ctx, cpu):
+    """Known answers: expectation_J / expectation_D
+    (ContinuousTimeMarkovModel.cpp:167-226), z-test at 5 sigma on 4e5 draws."""
+    r0, r1, T, n = 1.5, 0.5, 1.0, 400000
+    J0, J1, D0, D1 = cpu.expectations(r0, r1, T)
+    for a in (0, 1):
+        for b in (0, 1):
+            nj, j = ctx.end_cond_sample(r0, r1, a, b, T, 99 + 2*a + b, n, cap=48)
+            assert nj.max() < 48 and np.all((nj & 1) == (a != b))
+            k = np.arange(48)[None, :]
+            valid = k < nj[:, None]
+            # time in state a = sum of even segments; count jumps out of 0 / out of 1
+            t = np.where(valid, j, T)
+            seg = np.diff(np.concatenate([np.zeros((n, 1)), t, np.full((n, 1), T)], axis=1), axis=1)
+            even = (np.arange(seg.shape[1]) % 2 == 0)[None, :]
+            time_a = (seg*even).sum(1)
+            d0 = time_a if a == 0 else T - time_a
+            from_a = (nj + 1)//2
+            from_b = nj//2
+            j0 = from_a if a == 0 else from_b
+            j1 = from_b if a == 0 else from_a
+            for got, want in ((d0, D0[2*a + b]), (j0, J0[2*a + b]), (j1, J1[2*a + b])):
+                se = got.std()/np.sqrt(n) + 1e-12
+                assert abs(got.mean() - want) < 5*se, (a, b, got.mean(), want, se)
