@@ -1,0 +1,331 @@
+#!/usr/bin/env python
+"""bench.py -- MH site x branch updates per second of the MCMC E-step.
+
+A "step" is one call of the reference's SingleSiteSampler::run_mcmc with its default
+schedule (burn-in L=10 sweeps, then batch B=10 x (sweep + per-branch J/D pass);
+reference prog/epievo_est_params_histories.cpp:104-106, SingleSiteSampler.cpp:550-598)
+over one GPU's block of sites.  Updates per step = (L+B) * (n_sites-2) * n_branches.
+
+  value : paths already resident in HBM when the timed region starts (epv_run_mcmc)
+  e2e   : the same call with HOST buffers -- pinned host paths uploaded, E-step run,
+          paths + J/D read back, all inside the timed region
+  roofline : the colour-pass kernel (mh_pass_kernel), algorithmic bytes per launch
+          = (4/3) * n_sites * n_branches * (4 + 1/8 + 8*jbar)   
+          over its mean launch time from CUDA events around every launch
+  cpu_baseline : the unmodified reference (oracle/_ref) on one host core, bounded sample
+
+python bench.py --impl reference times the reference's CPU path on all host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "tests")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+METRIC = "mh_site_branch_updates_per_sec"
+UNIT = "updates/s"
+DEFAULT_SITES = {"bal8": 12_500_000, "testtree": 30_000_000, "pairwise": 1_000_000,
+                 "bal32": 3_000_000}
+WORKLOAD_DESC = {
+    "bal8": "north-star headline shard: balanced 8-leaf tree (14 branches x 0.05), "
+            "10^8 sites / 8 GPUs = 1.25e7 sites per GPU",
+    "testtree": "BASELINE config 4: reference test tree (4 branches), 3e7 sites",
+    "pairwise": "BASELINE config 2: single branch T=1.0, 1e6 sites",
+    "bal32": "BASELINE config 5 shard: balanced 32-leaf tree (62 branches x 0.05)",
+}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.FIELDS,
+                 "--format=csv,noheader,nounits", "-lms", "200"],
+                stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        try:
+            for line in open(self.path):
+                tok = [t.strip() for t in line.split(",")]
+                if len(tok) < 7:
+                    continue
+                try:
+                    sm.append(float(tok[0]))
+                    mx.append(float(tok[1]))
+                except ValueError:
+                    continue
+                for nm, val in zip(names, tok[3:7]):
+                    if val.lower().startswith("active"):
+                        reasons.add(nm)
+            os.unlink(self.path)
+        except Exception:
+            pass
+        if sm:
+            sm.sort()
+            out.update(sm_mhz=sm[len(sm) // 2], sm_max_mhz=max(mx), samples=len(sm))
+        out["reasons"] = sorted(reasons)
+        return out
+
+
+def run_reference(args):
+    """--impl reference: the unmodified reference CPU path on all host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import cpu_bench
+    procs = args.cpu_procs or (os.cpu_count() or 1)
+    n_s = args.cpu_sites
+    tree = cpu_bench.make_tree(args.workload)
+    n_br = tree.n_nodes - 1
+    sweeps = args.burn_in + args.batch
+    kind, per_step = cpu_bench.run(args.workload, n_s, args.burn_in, args.batch,
+                                   args.warmup + args.steps, procs)
+    timed = per_step[args.warmup:]
+    total_s = sum(timed)
+    updates = procs * (n_s - 2) * n_br * sweeps * args.steps
+    value = updates / total_s
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT,
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * total_s / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args, n_br, sample="%d processes x %d sites" % (procs, n_s)),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": procs, "kind": kind,
+                         "sample": "%d independent processes x %d-site blocks of the same workload, "
+                                   "each step one run_mcmc(L=%d,B=%d)" % (procs, n_s, args.burn_in, args.batch)},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def workload_config(args, n_br, sample=None):
+    cfg = {"workload": args.workload, "description": WORKLOAD_DESC[args.workload],
+           "n_sites_per_gpu": args.sites, "n_branches": n_br, "burn_in": args.burn_in,
+           "batch": args.batch, "step": "one run_mcmc E-step = (L+B) sweeps + B J/D passes",
+           "parallelism": "contiguous site blocks, one per GPU",
+           "l2": "inputs (>=0.5 GB of rows per pass) are larger than the 126 MB L2"}
+    if sample:
+        cfg["sample"] = sample
+    return cfg
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="bal8", choices=sorted(DEFAULT_SITES))
+    ap.add_argument("--sites", type=int, default=0, help="sites per GPU (default: per workload)")
+    ap.add_argument("--burn-in", type=int, default=10)
+    ap.add_argument("--batch", type=int, default=10)
+    ap.add_argument("--cpu-sites", type=int, default=25_000,
+                    help="sites per process of the CPU sample")
+    ap.add_argument("--cpu-procs", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    if not args.sites:
+        args.sites = DEFAULT_SITES[args.workload]
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import cpu_bench                      # make_tree / test_model helpers + the CPU leg
+    from epievo_b200.device import Context
+    from epievo_b200.synthetic import simulate_paths
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the B200 path has no CPU fallback "
+                         "(use --impl reference for the CPU reference arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    tree = cpu_bench.make_tree(args.workload)
+    rates, T = cpu_bench.test_model()
+    n_br = tree.n_nodes - 1
+    n = args.sites
+    sweeps = args.burn_in + args.batch
+    ps = simulate_paths(tree, n, rates, T, seed=12345 + rank)
+
+    # pinned host buffers in the C-ABI exchange format (jumps sized with headroom)
+    n_rows = n * tree.n_nodes
+    jcap = int(ps.jumps.size * 1.5) + 65536
+    h_init = torch.empty(n_rows, dtype=torch.uint8, pin_memory=True)
+    h_off = torch.empty(n_rows + 1, dtype=torch.int64, pin_memory=True)
+    h_jmp = torch.empty(jcap, dtype=torch.float64, pin_memory=True)
+    h_init.numpy()[:] = ps.init_state
+    h_off.numpy()[:] = ps.row_off.view(np.int64)
+    h_jmp.numpy()[:ps.jumps.size] = ps.jumps
+    tot_time = ps.tot_time.copy()
+    del ps
+
+    ctx = Context(local)
+    stream = torch.cuda.Stream()           # a real (non-default) stream the context launches on
+    torch.cuda.set_stream(stream)
+    ctx.set_stream(stream.cuda_stream)
+    ctx.set_tree(tree)
+    ctx.set_model(rates, T)
+    ctx.upload_raw(n, tree.n_nodes, h_init.data_ptr(), h_off.data_ptr(), h_jmp.data_ptr(), tot_time)
+    ctx.reset()
+
+    sweep_no = 0
+    for _ in range(args.warmup):
+        ctx.run_mcmc(args.burn_in, args.batch, seed=2024 + rank, first_sweep=sweep_no)
+        sweep_no += sweeps
+
+    # ---- timed region 1: device-resident E-steps ------------------------------------
+    ctx.enable_kernel_timing(True)
+    ctx.mh_kernel_time(reset=True)
+    clocks = ClockSampler(local)
+    launches0 = ctx.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    clocks.start()
+    e0.record(stream)
+    acc = 0.0
+    for _ in range(args.steps):
+        _, _, acc = ctx.run_mcmc(args.burn_in, args.batch, seed=2024 + rank, first_sweep=sweep_no)
+        sweep_no += sweeps
+    e1.record(stream)
+    barrier()
+    clk = clocks.stop()
+    ms = e0.elapsed_time(e1)
+    mh_ms, mh_launches = ctx.mh_kernel_time(reset=True)
+    ctx.enable_kernel_timing(False)
+    launches = ctx.launch_count() - launches0
+    jc = ctx.jump_counts()
+    jbar = float(jc.sum()) / (n * n_br)
+
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    updates_per_step = world * (n - 2) * n_br * sweeps
+    value = updates_per_step * args.steps / (ms_max * 1e-3)
+
+    # ---- timed region 2: end to end through the C-ABI with host buffers --------------
+    e2e = None
+    if not args.no_e2e:
+        n_sites_, n_nodes_, nj = ctx.paths_size()
+        if nj > jcap:
+            raise SystemExit("bench.py: pinned jump buffer too small")
+        ctx.download_raw(h_init.data_ptr(), h_off.data_ptr(), h_jmp.data_ptr())
+        h2d = d2h = 0
+        barrier()
+        e0.record(stream)
+        for _ in range(args.steps):
+            nj_in = int(h_off[n_rows].item())
+            ctx.upload_raw(n, tree.n_nodes, h_init.data_ptr(), h_off.data_ptr(), h_jmp.data_ptr(), tot_time)
+            J, D, acc2 = ctx.run_mcmc(args.burn_in, args.batch, seed=2024 + rank, first_sweep=sweep_no)
+            sweep_no += sweeps
+            _, _, nj_out = ctx.paths_size()
+            if nj_out > jcap:
+                raise SystemExit("bench.py: pinned jump buffer too small")
+            ctx.download_raw(h_init.data_ptr(), h_off.data_ptr(), h_jmp.data_ptr())
+            h2d += n_rows + 8 * (n_rows + 1) + 8 * nj_in
+            d2h += n_rows + 8 * (n_rows + 1) + 8 * nj_out + 2 * 8 * 8 * tree.n_nodes
+        e1.record(stream)
+        barrier()
+        t2 = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+        e2e = {"value": updates_per_step * args.steps / (float(t2.item()) * 1e-3), "unit": UNIT,
+               "h2d_bytes_per_step": h2d // args.steps, "d2h_bytes_per_step": d2h // args.steps,
+               "ms_per_step": float(t2.item()) / args.steps,
+               "call": "epv_upload_paths + epv_run_mcmc + epv_download_paths (pinned host buffers)"}
+
+    # ---- roofline of the dominant kernel -----------------------------------------------
+    peaks_file = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_file):
+        peak, peak_src = float(json.load(open(peaks_file))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    row_bytes = 4.0 + 0.125 + 8.0 * jbar
+    bytes_per_launch = (4.0 / 3.0) * n * n_br * row_bytes
+    avg_launch_ms = mh_ms / max(1, mh_launches)
+    achieved = bytes_per_launch / (avg_launch_ms * 1e-3) / 1e9 if avg_launch_ms > 0 else 0.0
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None, "kernel": "mh_pass_kernel",
+                "peak_source": peak_src, "avg_launch_ms": avg_launch_ms, "launches_timed": mh_launches,
+                "algorithmic_bytes_per_launch": bytes_per_launch, "jumps_per_row": jbar,
+                "kernel_share_of_step": mh_ms / ms if ms > 0 else None}
+
+    # ---- CPU baseline (rank 0, N=1 only) ---------------------------------------------------
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        n_s = 50_000
+        bi, ba = 5, 5
+        kind, per_step = cpu_bench.run(args.workload, n_s, bi, ba, 1, 1)
+        cpu_baseline = {"value": (n_s - 2) * n_br * (bi + ba) / per_step[0], "unit": UNIT, "cores": 1,
+                        "kind": kind,
+                        "sample": "%d sites of the same workload, one run_mcmc(L=%d,B=%d), single "
+                                  "thread (the reference is single-threaded), %.1f s" % (n_s, bi, ba, per_step[0])}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(args, n_br), "clocks": clk, "e2e": e2e,
+            "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu_baseline,
+            "acc_rate": acc,
+        }
+        print(json.dumps(line))
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -70,6 +70,8 @@ int epv_create(epv_ctx **out, int device) {
     && cudaMallocHost(&c->h_mail, 4096*sizeof(unsigned long long)) == cudaSuccess
     && cudaMalloc(&c->d_scratch, (size_t)c->scratch_slots*c->scratch_cap*sizeof(double)) == cudaSuccess
     && cudaEventCreate(&c->ev0) == cudaSuccess && cudaEventCreate(&c->ev1) == cudaSuccess;
+  for (int k = 0; ok && k < 2*epv_ctx::EV_RING; ++k)
+    ok = cudaEventCreate(&c->ev_ring[k]) == cudaSuccess;
   if (ok) {
     c->stream = c->own_stream;
     cudaMemset(c->d_err, 0, sizeof(unsigned));
@@ -97,6 +99,7 @@ void epv_destroy(epv_ctx *c) {
   cudaFree(c->d_J); cudaFree(c->d_D); cudaFree(c->d_Jsum); cudaFree(c->d_Dsum); cudaFree(c->d_ss);
   for (int k = 0; k < 4; ++k) cudaFree(c->d_halo[k]);
   cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1);
+  for (int k = 0; k < 2*epv_ctx::EV_RING; ++k) if (c->ev_ring[k]) cudaEventDestroy(c->ev_ring[k]);
   cudaStreamDestroy(c->own_stream);
   delete c;
 }

@@ -29,6 +29,17 @@ void interior(const epv_ctx *c, uint64_t &lo, uint64_t &hi) {
   if (g0 + (int64_t)hi > (int64_t)c->n_global - 1) hi = (uint64_t)((int64_t)c->n_global - 1 - g0);
 }
 
+// Resolve the pending (start, stop) event pairs of the colour-pass launches.
+void drain_timing(epv_ctx *c) {
+  if (!c->ev_pending) return;
+  cudaEventSynchronize(c->ev_ring[2*c->ev_pending - 1]);
+  for (int k = 0; k < c->ev_pending; ++k) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, c->ev_ring[2*k], c->ev_ring[2*k + 1]) == cudaSuccess) c->mh_ms += ms;
+  }
+  c->ev_pending = 0;
+}
+
 int do_reset(epv_ctx *c) {
   launch_tri_llh(c->mp, c->view(c->cur), c->d_state, c->W, c->tree(), c->n_sites, c->d_tri, c->stream);
   ++c->launches;
@@ -56,13 +67,14 @@ int one_pass(epv_ctx *c, int colour, uint64_t seed, uint32_t sweep) {
   a.scratch_slots = c->scratch_slots; a.scratch_cap = c->scratch_cap;
   a.err = c->d_err; a.n_accept = c->d_nacc;
   EPV_CUDA(c, cudaMemsetAsync(c->d_scratch_ctr, 0, sizeof(uint32_t), c->stream));
-  if (c->timing) cudaEventRecord(c->ev0, c->stream);
+  if (c->timing) {
+    if (c->ev_pending == epv_ctx::EV_RING) drain_timing(c);
+    cudaEventRecord(c->ev_ring[2*c->ev_pending], c->stream);
+  }
   launch_mh_pass(a, c->stream);
   if (c->timing) {
-    cudaEventRecord(c->ev1, c->stream);
-    cudaEventSynchronize(c->ev1);
-    float ms = 0.f; cudaEventElapsedTime(&ms, c->ev0, c->ev1);
-    c->mh_ms += ms;
+    cudaEventRecord(c->ev_ring[2*c->ev_pending + 1], c->stream);
+    ++c->ev_pending;
   }
   ++c->launches; ++c->mh_launches;
   c->ticket_base += c->n_tiles;
@@ -221,10 +233,17 @@ int epv_scale_jump_times(epv_ctx *c, const double *new_branches) {
 
 uint64_t epv_launch_count(const epv_ctx *c) { return c ? c->launches : 0; }
 
-int epv_enable_kernel_timing(epv_ctx *c, int on) { if (!c) return 1; c->timing = on != 0; return 0; }
+int epv_enable_kernel_timing(epv_ctx *c, int on) {
+  if (!c) return 1;
+  if (!on) drain_timing(c);
+  c->timing = on != 0;
+  return 0;
+}
 
 int epv_mh_kernel_time(epv_ctx *c, int reset, double *ms, uint64_t *launches) {
   if (!c) return 1;
+  cudaSetDevice(c->device);
+  drain_timing(c);
   if (ms) *ms = c->mh_ms;
   if (launches) *launches = c->mh_launches;
   if (reset) { c->mh_ms = 0.0; c->mh_launches = 0; }

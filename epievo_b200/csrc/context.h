@@ -63,6 +63,11 @@ struct epv_ctx {
   bool timing = false;
   double mh_ms = 0.0;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  // ring of (start, stop) event pairs around the colour-pass launches; resolved
+  // lazily (after the per-sweep stream sync) so timing never stalls the stream
+  static constexpr int EV_RING = 96;
+  cudaEvent_t ev_ring[2*EV_RING] = {};
+  int ev_pending = 0;
 
   epv::PathView view(int which) const {
     epv::PathView v; v.off = d_off[which]; v.jmp = d_jmp[which]; v.jbase = d_jbase;
