@@ -138,7 +138,8 @@ def workload_config(args, n_br, sample=None):
     cfg = {"workload": args.workload, "description": WORKLOAD_DESC[args.workload],
            "n_sites_per_gpu": args.sites, "n_branches": n_br, "burn_in": args.burn_in,
            "batch": args.batch, "step": "one run_mcmc E-step = (L+B) sweeps + B J/D passes",
-           "parallelism": "contiguous site blocks, one per GPU",
+           "parallelism": "contiguous site blocks, one per GPU; 3-site halos, one NCCL send/recv pair "
+                          "per neighbour per colour pass, one all-reduce of J/D per E-step",
            "l2": "inputs (>=0.5 GB of rows per pass) are larger than the 126 MB L2"}
     if sample:
         cfg["sample"] = sample
@@ -193,9 +194,20 @@ def main():
     tree = cpu_bench.make_tree(args.workload)
     rates, T = cpu_bench.test_model()
     n_br = tree.n_nodes - 1
-    n = args.sites
     sweeps = args.burn_in + args.batch
-    ps = simulate_paths(tree, n, rates, T, seed=12345 + rank)
+    from epievo_b200 import sharded as S
+    from epievo_b200.paths import PathSet
+    n_global = args.sites * world
+    lo, hi, halo_lo, halo_hi = S.shard_bounds(n_global, world, rank)
+    n_own = hi - lo
+    ps = simulate_paths(tree, n_own, rates, T, seed=12345 + rank)
+    if world > 1:
+        # neighbours' boundary sites become this rank's halos (gathered once, at setup)
+        edges = [None] * world
+        dist.all_gather_object(edges, (ps.site_slice(0, S.HALO), ps.site_slice(n_own - S.HALO, n_own)))
+        parts = ([edges[rank - 1][1]] if halo_lo else []) + [ps] + ([edges[rank + 1][0]] if halo_hi else [])
+        ps = PathSet.concat_sites(parts)
+    n = ps.n_sites                          # local sites: owned block + halos
 
     # pinned host buffers in the C-ABI exchange format (jumps sized with headroom)
     n_rows = n * tree.n_nodes
@@ -215,12 +227,24 @@ def main():
     ctx.set_stream(stream.cuda_stream)
     ctx.set_tree(tree)
     ctx.set_model(rates, T)
+    shard = transport = None
+    if world > 1:
+        shard = S.Shard(ctx, n_global, world, rank, torch.device("cuda", local))
+        transport = S.DistExchange(shard)
     ctx.upload_raw(n, tree.n_nodes, h_init.data_ptr(), h_off.data_ptr(), h_jmp.data_ptr(), tot_time)
     ctx.reset()
 
+    def e_step(first_sweep):
+        """One E-step = run_mcmc(L, B).  N=1: the C-ABI call; N>1: the same schedule with a
+        halo exchange after every colour pass and one all-reduce of the J/D sums."""
+        if world == 1:
+            return ctx.run_mcmc(args.burn_in, args.batch, seed=2024, first_sweep=first_sweep)
+        return S.run_mcmc([shard], transport, args.burn_in, args.batch, seed=2024,
+                          first_sweep=first_sweep, allreduce=transport.allreduce_sum)
+
     sweep_no = 0
     for _ in range(args.warmup):
-        ctx.run_mcmc(args.burn_in, args.batch, seed=2024 + rank, first_sweep=sweep_no)
+        e_step(sweep_no)
         sweep_no += sweeps
 
     # ---- timed region 1: device-resident E-steps ------------------------------------
@@ -234,7 +258,7 @@ def main():
     e0.record(stream)
     acc = 0.0
     for _ in range(args.steps):
-        _, _, acc = ctx.run_mcmc(args.burn_in, args.batch, seed=2024 + rank, first_sweep=sweep_no)
+        _, _, acc = e_step(sweep_no)
         sweep_no += sweeps
     e1.record(stream)
     barrier()
@@ -244,13 +268,13 @@ def main():
     ctx.enable_kernel_timing(False)
     launches = ctx.launch_count() - launches0
     jc = ctx.jump_counts()
-    jbar = float(jc.sum()) / (n * n_br)
+    jbar = float(jc.sum()) / (n_own * n_br)
 
     t = torch.tensor([ms], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_max = float(t.item())
-    updates_per_step = world * (n - 2) * n_br * sweeps
+    updates_per_step = (n_global - 2) * n_br * sweeps
     value = updates_per_step * args.steps / (ms_max * 1e-3)
 
     # ---- timed region 2: end to end through the C-ABI with host buffers --------------
@@ -266,7 +290,7 @@ def main():
         for _ in range(args.steps):
             nj_in = int(h_off[n_rows].item())
             ctx.upload_raw(n, tree.n_nodes, h_init.data_ptr(), h_off.data_ptr(), h_jmp.data_ptr(), tot_time)
-            J, D, acc2 = ctx.run_mcmc(args.burn_in, args.batch, seed=2024 + rank, first_sweep=sweep_no)
+            J, D, acc2 = e_step(sweep_no)
             sweep_no += sweeps
             _, _, nj_out = ctx.paths_size()
             if nj_out > jcap:
@@ -291,7 +315,7 @@ def main():
     else:
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
     row_bytes = 4.0 + 0.125 + 8.0 * jbar
-    bytes_per_launch = (4.0 / 3.0) * n * n_br * row_bytes
+    bytes_per_launch = (4.0 / 3.0) * n_own * n_br * row_bytes
     avg_launch_ms = mh_ms / max(1, mh_launches)
     achieved = bytes_per_launch / (avg_launch_ms * 1e-3) / 1e9 if avg_launch_ms > 0 else 0.0
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",

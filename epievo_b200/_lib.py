@@ -39,6 +39,9 @@ SIGNATURES = {
     "epv_scale_jump_times": (C.c_int, [ctx_p, dp]),
     "epv_pass": (C.c_int, [ctx_p, C.c_int, u64, u64]),
     "epv_accept_count": (C.c_int, [ctx_p, C.c_int, u64p]),
+    "epv_halo_record_bytes": (C.c_int, [ctx_p, u64p]),
+    "epv_halo_pack": (C.c_int, [ctx_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "epv_halo_unpack": (C.c_int, [ctx_p, C.c_int, C.c_void_p, C.c_void_p]),
     "epv_site_debug": (C.c_int, [ctx_p, u64, u64, u64p, u64p, dp, dp, u64p, u64p, dp, dp, dp,
                                  dp, dp]),
     "epv_get_tri_llh": (C.c_int, [ctx_p, dp]),

@@ -21,7 +21,9 @@ void free_paths(epv_ctx *c) {
     cudaFree(c->d_jmp[k]); c->d_jmp[k] = nullptr;
   }
   cudaFree(c->d_jbase); cudaFree(c->d_jcap); cudaFree(c->d_state); cudaFree(c->d_tri);
-  cudaFree(c->d_desc);
+  cudaFree(c->d_desc); cudaFree(c->d_hcnt); cudaFree(c->d_hjmp);
+  cudaFree(c->d_stage_init); cudaFree(c->d_stage_off);
+  c->d_hcnt = nullptr; c->d_hjmp = nullptr; c->d_stage_init = nullptr; c->d_stage_off = nullptr;
   c->d_jbase = c->d_jcap = nullptr; c->d_state = nullptr; c->d_tri = nullptr;
   c->d_desc = nullptr;
   c->n_sites = 0; c->tri_valid = false; c->stats_valid = false;
@@ -39,6 +41,8 @@ int check_device_flags(epv_ctx *c) {
   if (flags & ERR_SCRATCH_SIZE) m += " a proposed path exceeds the per-site scratch capacity;";
   if (flags & ERR_SAMPLER_STUCK) m += " end-conditioned sampler did not terminate;";
   if (flags & ERR_BAD_INPUT) m += " malformed input;";
+  if (flags & ERR_HALO_CAPACITY) m += " a shard-boundary row has more jumps than a halo record holds;";
+  if (flags & ERR_HALO_MISMATCH) m += " a halo record arrived for the wrong site (driver / colour mismatch);";
   return fail(c, m + " paths on the device are no longer valid");
 }
 
@@ -97,7 +101,6 @@ void epv_destroy(epv_ctx *c) {
   cudaFree(c->d_err); cudaFree(c->d_nacc); cudaFree(c->d_ticket); cudaFree(c->d_scratch_ctr);
   cudaFree(c->d_scratch); cudaFree(c->d_out9); cudaFree(c->d_mail); cudaFreeHost(c->h_mail);
   cudaFree(c->d_J); cudaFree(c->d_D); cudaFree(c->d_Jsum); cudaFree(c->d_Dsum); cudaFree(c->d_ss);
-  for (int k = 0; k < 4; ++k) cudaFree(c->d_halo[k]);
   cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1);
   for (int k = 0; k < 2*epv_ctx::EV_RING; ++k) if (c->ev_ring[k]) cudaEventDestroy(c->ev_ring[k]);
   cudaStreamDestroy(c->own_stream);
@@ -174,11 +177,15 @@ int epv_set_shard(epv_ctx *c, uint64_t n_global, uint64_t site_begin, uint64_t s
                   uint64_t halo_lo, uint64_t halo_hi) {
   if (!c) return 1;
   if (c->n_sites) return fail(c, "set the shard before uploading paths");
-  if (site_begin % 3 || halo_lo % 3) return fail(c, "site_begin and halo_lo must be multiples of 3");
+  if (site_begin % 3) return fail(c, "site_begin must be a multiple of 3 (colour alignment)");
   if (site_end <= site_begin || site_end > n_global || halo_lo > site_begin
       || site_end + halo_hi > n_global)
     return fail(c, "inconsistent shard bounds");
-  if ((halo_lo && halo_lo < 3) || (halo_hi && halo_hi < 2)) return fail(c, "halo must cover at least 2 sites");
+  if ((halo_lo != 0 && halo_lo != HALO_W) || (halo_hi != 0 && halo_hi != HALO_W))
+    return fail(c, "halo_lo / halo_hi must be 0 (global end) or 3 sites");
+  if ((site_begin > 0) != (halo_lo != 0) || (site_end < n_global) != (halo_hi != 0))
+    return fail(c, "a shard needs a 3-site halo on every side that has a neighbour");
+  if (site_end - site_begin < 2*HALO_W) return fail(c, "a shard must own at least 6 sites");
   c->have_shard = true;
   c->n_global = n_global; c->site_begin = site_begin; c->site_end = site_end;
   c->halo_lo = halo_lo; c->halo_hi = halo_hi;

@@ -15,7 +15,7 @@ int read_branch_totals(epv_ctx *c, std::vector<uint64_t> &tot) {
   tot.assign(n_br, 0);
   for (int bi = 0; bi < n_br; ++bi)
     EPV_CUDA(c, cudaMemcpyAsync(reinterpret_cast<uint32_t *>(c->h_mail) + bi,
-                                c->d_off[c->cur] + (uint64_t)bi*c->off_pitch + c->n_sites,
+                                c->d_off[c->cur] + (uint64_t)bi*c->off_pitch + c->n_own(),
                                 sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
   EPV_CUDA(c, cudaStreamSynchronize(c->stream));
   for (int bi = 0; bi < n_br; ++bi) tot[bi] = reinterpret_cast<uint32_t *>(c->h_mail)[bi];
@@ -50,7 +50,7 @@ int maybe_regrow(epv_ctx *c, const std::vector<uint64_t> &tot) {
     else if (4*tot[bi] > 3*c->h_jcap[bi]) need = true;
   if (!need) return 0;
   std::vector<uint64_t> cap(n_br), base;
-  for (int bi = 0; bi < n_br; ++bi) cap[bi] = std::max(c->h_jcap[bi], capacity_for(2*tot[bi], c->n_sites));
+  for (int bi = 0; bi < n_br; ++bi) cap[bi] = std::max(c->h_jcap[bi], capacity_for(2*tot[bi], c->n_own()));
   double *nj[2]; uint64_t total;
   if (int r = alloc_jumps(c, cap, nj, base, total)) return r;
   for (int bi = 0; bi < n_br; ++bi)
@@ -63,6 +63,26 @@ int maybe_regrow(epv_ctx *c, const std::vector<uint64_t> &tot) {
   c->d_jmp[0] = nj[0]; c->d_jmp[1] = nj[1];
   c->h_jbase = base; c->h_jcap = cap; c->jmp_total_cap = total;
   return 0;
+}
+
+}  // namespace epv
+
+namespace epv {
+
+// Host copy of the halo store: counts [2*HALO_W][n_br] and jumps [..][HALO_K].
+int read_halo_store(epv_ctx *c, std::vector<uint16_t> &cnt, std::vector<double> &jmp) {
+  const size_t n_br = c->n_nodes - 1, rows = 2*HALO_W*n_br;
+  cnt.assign(rows, 0); jmp.assign(rows*HALO_K, 0.0);
+  EPV_CUDA(c, cudaMemcpyAsync(cnt.data(), c->d_hcnt, rows*sizeof(uint16_t), cudaMemcpyDeviceToHost, c->stream));
+  EPV_CUDA(c, cudaMemcpyAsync(jmp.data(), c->d_hjmp, rows*HALO_K*sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  EPV_CUDA(c, cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+// Local site of halo slot k (0..2 low halo, 3..5 high halo), or -1 if the slot is unused.
+static int64_t slot_site(const epv_ctx *c, int k) {
+  if (k < HALO_W) return (uint64_t)k < c->halo_lo ? k : -1;
+  return (uint64_t)(k - HALO_W) < c->halo_hi ? (int64_t)(c->n_sites - c->halo_hi) + (k - HALO_W) : -1;
 }
 
 }  // namespace epv
@@ -86,52 +106,94 @@ int epv_upload_paths(epv_ctx *c, uint64_t n_sites, uint64_t n_nodes, const uint8
     if (tot_time[b] != c->h_branch[b])
       return fail(c, "paths' tot_time differs from the tree's branch length (the reference "
                      "asserts equality, Segment.cpp:76); rescale the paths or the tree");
-  EPV_CUDA(c, cudaStreamSynchronize(c->stream));
-  free_paths(c);
-
-  std::vector<uint64_t> count(n_br), cap(n_br);
   if (row_off[0] != 0 || row_off[n_sites] != row_off[0]) return fail(c, "root rows must be empty");
+  const uint64_t own_lo = c->halo_lo, own_hi = n_sites - c->halo_hi, n_own = own_hi - own_lo;
+  std::vector<uint64_t> count(n_br), first(n_br);
   for (int bi = 0; bi < n_br; ++bi) {
-    const uint64_t a = row_off[(uint64_t)(bi + 1)*n_sites], b = row_off[(uint64_t)(bi + 2)*n_sites];
-    if (b < a) return fail(c, "row_off must be non-decreasing");
-    count[bi] = b - a;
+    const uint64_t r = (uint64_t)(bi + 1)*n_sites;
+    if (row_off[r + n_sites] < row_off[r]) return fail(c, "row_off must be non-decreasing");
+    first[bi] = row_off[r + own_lo];
+    count[bi] = row_off[r + own_hi] - first[bi];
     if (count[bi] > 0xfffffff0ull) return fail(c, "a branch holds more than 2^32 jumps on one GPU; use more shards");
-    cap[bi] = capacity_for(count[bi], n_sites);
   }
-  c->n_sites = n_sites;
-  c->W = (c->n_nodes + 7)/8;
-  c->off_pitch = (n_sites + 1 + 31) & ~31ull;
-  c->n_tiles = (uint32_t)(((n_sites + 2)/3 + MH_THREADS - 1)/MH_THREADS);
-  if (int r = alloc_jumps(c, cap, c->d_jmp, c->h_jbase, c->jmp_total_cap)) return r;
-  c->h_jcap = cap;
-  for (int k = 0; k < 2; ++k)
-    EPV_CUDA(c, cudaMalloc(&c->d_off[k], (size_t)n_br*c->off_pitch*sizeof(uint32_t)));
-  EPV_CUDA(c, cudaMalloc(&c->d_jbase, n_br*sizeof(uint64_t)));
-  EPV_CUDA(c, cudaMalloc(&c->d_jcap, n_br*sizeof(uint64_t)));
-  EPV_CUDA(c, cudaMalloc(&c->d_state, (size_t)n_sites*c->W));
-  EPV_CUDA(c, cudaMalloc(&c->d_tri, n_sites*sizeof(double)));
-  EPV_CUDA(c, cudaMalloc(&c->d_desc, (size_t)n_br*c->n_tiles*sizeof(unsigned long long)));
-  EPV_CUDA(c, cudaMemsetAsync(c->d_desc, 0, (size_t)n_br*c->n_tiles*sizeof(unsigned long long), c->stream));
-  c->epoch = 0; c->cur = 0;
-  EPV_CUDA(c, cudaMemcpyAsync(c->d_jbase, c->h_jbase.data(), n_br*sizeof(uint64_t), cudaMemcpyHostToDevice, c->stream));
-  EPV_CUDA(c, cudaMemcpyAsync(c->d_jcap, c->h_jcap.data(), n_br*sizeof(uint64_t), cudaMemcpyHostToDevice, c->stream));
+  EPV_CUDA(c, cudaStreamSynchronize(c->stream));
+
+  // (re)allocate only when the shape changed or a branch no longer fits
+  bool fits = c->n_sites == n_sites && c->d_off[0] && (int)c->h_jcap.size() == n_br;
+  for (int bi = 0; fits && bi < n_br; ++bi) fits = 4*count[bi] <= 3*c->h_jcap[bi];
+  if (!fits) {
+    free_paths(c);
+    std::vector<uint64_t> cap(n_br);
+    for (int bi = 0; bi < n_br; ++bi) cap[bi] = capacity_for(count[bi], n_own);
+    c->n_sites = n_sites;
+    c->W = (c->n_nodes + 7)/8;
+    c->off_pitch = (n_own + 1 + 31) & ~31ull;
+    c->n_tiles = (uint32_t)(((n_sites + 2)/3 + MH_THREADS - 1)/MH_THREADS);
+    if (int r = alloc_jumps(c, cap, c->d_jmp, c->h_jbase, c->jmp_total_cap)) return r;
+    c->h_jcap = cap;
+    for (int k = 0; k < 2; ++k)
+      EPV_CUDA(c, cudaMalloc(&c->d_off[k], (size_t)n_br*c->off_pitch*sizeof(uint32_t)));
+    EPV_CUDA(c, cudaMalloc(&c->d_jbase, n_br*sizeof(uint64_t)));
+    EPV_CUDA(c, cudaMalloc(&c->d_jcap, n_br*sizeof(uint64_t)));
+    EPV_CUDA(c, cudaMalloc(&c->d_state, (size_t)n_sites*c->W));
+    EPV_CUDA(c, cudaMalloc(&c->d_tri, n_sites*sizeof(double)));
+    EPV_CUDA(c, cudaMalloc(&c->d_desc, (size_t)n_br*c->n_tiles*sizeof(unsigned long long)));
+    EPV_CUDA(c, cudaMalloc(&c->d_hcnt, (size_t)2*HALO_W*n_br*sizeof(uint16_t)));
+    EPV_CUDA(c, cudaMalloc(&c->d_hjmp, (size_t)2*HALO_W*n_br*HALO_K*sizeof(double)));
+    const uint64_t n_rows = n_nodes*n_sites;
+    EPV_CUDA(c, cudaMalloc(&c->d_stage_init, n_rows));
+    EPV_CUDA(c, cudaMalloc(&c->d_stage_off, (n_rows + 1)*sizeof(unsigned long long)));
+    EPV_CUDA(c, cudaMemsetAsync(c->d_desc, 0, (size_t)n_br*c->n_tiles*sizeof(unsigned long long), c->stream));
+    c->epoch = 0;
+    EPV_CUDA(c, cudaMemcpyAsync(c->d_jbase, c->h_jbase.data(), n_br*sizeof(uint64_t), cudaMemcpyHostToDevice, c->stream));
+    EPV_CUDA(c, cudaMemcpyAsync(c->d_jcap, c->h_jcap.data(), n_br*sizeof(uint64_t), cudaMemcpyHostToDevice, c->stream));
+  }
+  c->cur = 0; c->tri_valid = false; c->stats_valid = false;
 
   // raw host arrays -> device staging -> layout conversion on the device
-  uint8_t *t_init = nullptr; unsigned long long *t_off = nullptr;
   const uint64_t n_rows = n_nodes*n_sites;
-  EPV_CUDA(c, cudaMalloc(&t_init, n_rows));
-  EPV_CUDA(c, cudaMalloc(&t_off, (n_rows + 1)*sizeof(unsigned long long)));
-  EPV_CUDA(c, cudaMemcpyAsync(t_init, init_state, n_rows, cudaMemcpyHostToDevice, c->stream));
-  EPV_CUDA(c, cudaMemcpyAsync(t_off, row_off, (n_rows + 1)*sizeof(unsigned long long), cudaMemcpyHostToDevice, c->stream));
-  launch_import(t_init, t_off, n_sites, c->n_nodes, c->d_off[0], c->off_pitch, c->d_state, c->W, c->stream);
+  EPV_CUDA(c, cudaMemcpyAsync(c->d_stage_init, init_state, n_rows, cudaMemcpyHostToDevice, c->stream));
+  EPV_CUDA(c, cudaMemcpyAsync(c->d_stage_off, row_off, (n_rows + 1)*sizeof(unsigned long long), cudaMemcpyHostToDevice, c->stream));
+  launch_import(c->d_stage_init, c->d_stage_off, n_sites, c->n_nodes, own_lo, n_own, c->d_off[0],
+                c->off_pitch, c->d_state, c->W, c->stream);
   ++c->launches;
   for (int bi = 0; bi < n_br; ++bi)
     if (count[bi])
-      EPV_CUDA(c, cudaMemcpyAsync(c->d_jmp[0] + c->h_jbase[bi], jumps + row_off[(uint64_t)(bi + 1)*n_sites],
+      EPV_CUDA(c, cudaMemcpyAsync(c->d_jmp[0] + c->h_jbase[bi], jumps + first[bi],
                                   count[bi]*sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  // halo rows -> fixed-capacity halo store
+  std::vector<uint16_t> hc((size_t)2*HALO_W*n_br, 0);
+  std::vector<double> hj((size_t)2*HALO_W*n_br*HALO_K, 0.0);
+  for (int k = 0; k < 2*HALO_W; ++k) {
+    const int64_t s = slot_site(c, k);
+    if (s < 0) continue;
+    for (int bi = 0; bi < n_br; ++bi) {
+      const uint64_t r = (uint64_t)(bi + 1)*n_sites + (uint64_t)s;
+      const uint64_t n = row_off[r + 1] - row_off[r];
+      if (n > HALO_K) return fail(c, "a halo row holds more jumps than the halo store's per-row capacity");
+      hc[(size_t)k*n_br + bi] = (uint16_t)n;
+      std::memcpy(&hj[((size_t)k*n_br + bi)*HALO_K], jumps + row_off[r], n*sizeof(double));
+    }
+  }
+  EPV_CUDA(c, cudaMemcpyAsync(c->d_hcnt, hc.data(), hc.size()*sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream));
+  EPV_CUDA(c, cudaMemcpyAsync(c->d_hjmp, hj.data(), hj.size()*sizeof(double), cudaMemcpyHostToDevice, c->stream));
   EPV_CUDA(c, cudaStreamSynchronize(c->stream));
-  cudaFree(t_init); cudaFree(t_off);
   EPV_CUDA(c, cudaGetLastError());
+  return 0;
+}
+
+// Jumps held per branch: halo-low rows, owned rows, halo-high rows.
+static int branch_jump_layout(epv_ctx *c, std::vector<uint64_t> &own, std::vector<uint16_t> &hc,
+                              std::vector<double> &hj, std::vector<uint64_t> &prefix) {
+  const int n_br = c->n_nodes - 1;
+  if (int r = read_branch_totals(c, own)) return r;
+  if (int r = read_halo_store(c, hc, hj)) return r;
+  prefix.assign(n_br + 1, 0);
+  for (int bi = 0; bi < n_br; ++bi) {
+    uint64_t t = own[bi];
+    for (int k = 0; k < 2*HALO_W; ++k) if (slot_site(c, k) >= 0) t += hc[(size_t)k*n_br + bi];
+    prefix[bi + 1] = prefix[bi] + t;
+  }
   return 0;
 }
 
@@ -139,13 +201,11 @@ int epv_paths_size(epv_ctx *c, uint64_t *n_sites, uint64_t *n_nodes, uint64_t *n
   if (!c) return 1;
   if (!c->n_sites) return fail(c, "no paths loaded");
   cudaSetDevice(c->device);
-  std::vector<uint64_t> tot;
-  if (int r = read_branch_totals(c, tot)) return r;
-  uint64_t s = 0;
-  for (uint64_t t : tot) s += t;
+  std::vector<uint64_t> own, prefix; std::vector<uint16_t> hc; std::vector<double> hj;
+  if (int r = branch_jump_layout(c, own, hc, hj, prefix)) return r;
   if (n_sites) *n_sites = c->n_sites;
   if (n_nodes) *n_nodes = (uint64_t)c->n_nodes;
-  if (n_jumps) *n_jumps = s;
+  if (n_jumps) *n_jumps = prefix.back();
   return 0;
 }
 
@@ -156,7 +216,7 @@ int epv_jump_counts(epv_ctx *c, uint64_t *per_node) {
   std::vector<uint64_t> tot;
   if (int r = read_branch_totals(c, tot)) return r;
   per_node[0] = 0;
-  for (int bi = 0; bi + 1 < c->n_nodes; ++bi) per_node[bi + 1] = tot[bi];
+  for (int bi = 0; bi + 1 < c->n_nodes; ++bi) per_node[bi + 1] = tot[bi];   // owned rows only
   return 0;
 }
 
@@ -167,27 +227,35 @@ int epv_download_paths(epv_ctx *c, uint8_t *init_state, uint64_t *row_off, doubl
   cudaSetDevice(c->device);
   if (int r = check_device_flags(c)) return r;
   const int n_br = c->n_nodes - 1;
-  std::vector<uint64_t> tot;
-  if (int r = read_branch_totals(c, tot)) return r;
-  std::vector<uint64_t> prefix(n_br + 1, 0);
-  for (int bi = 0; bi < n_br; ++bi) prefix[bi + 1] = prefix[bi] + tot[bi];
+  std::vector<uint64_t> own, prefix; std::vector<uint16_t> hc; std::vector<double> hj;
+  if (int r = branch_jump_layout(c, own, hc, hj, prefix)) return r;
   const uint64_t n_rows = (uint64_t)c->n_nodes*c->n_sites;
-  uint8_t *t_init = nullptr; unsigned long long *t_off = nullptr; uint64_t *t_pre = nullptr;
-  EPV_CUDA(c, cudaMalloc(&t_init, n_rows));
-  EPV_CUDA(c, cudaMalloc(&t_off, (n_rows + 1)*sizeof(unsigned long long)));
-  EPV_CUDA(c, cudaMalloc(&t_pre, (n_br + 1)*sizeof(uint64_t)));
+  uint64_t *t_pre = reinterpret_cast<uint64_t *>(c->d_mail);
+  if ((size_t)n_br + 1 > 4096) return fail(c, "too many branches");
   EPV_CUDA(c, cudaMemcpyAsync(t_pre, prefix.data(), (n_br + 1)*sizeof(uint64_t), cudaMemcpyHostToDevice, c->stream));
-  launch_export(c->d_off[c->cur], c->off_pitch, c->d_state, c->W, c->n_sites, c->n_nodes, t_pre,
-                t_init, t_off, c->stream);
+  launch_export(c->view(c->cur), c->d_state, c->W, c->n_sites, c->n_nodes, t_pre,
+                c->d_stage_init, c->d_stage_off, c->stream);
   ++c->launches;
-  EPV_CUDA(c, cudaMemcpyAsync(init_state, t_init, n_rows, cudaMemcpyDeviceToHost, c->stream));
-  EPV_CUDA(c, cudaMemcpyAsync(row_off, t_off, (n_rows + 1)*sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
-  for (int bi = 0; bi < n_br; ++bi)
-    if (tot[bi])
-      EPV_CUDA(c, cudaMemcpyAsync(jumps + prefix[bi], c->d_jmp[c->cur] + c->h_jbase[bi],
-                                  tot[bi]*sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  EPV_CUDA(c, cudaMemcpyAsync(init_state, c->d_stage_init, n_rows, cudaMemcpyDeviceToHost, c->stream));
+  EPV_CUDA(c, cudaMemcpyAsync(row_off, c->d_stage_off, (n_rows + 1)*sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+  for (int bi = 0; bi < n_br; ++bi) {
+    double *dst = jumps + prefix[bi];
+    for (int k = 0; k < HALO_W; ++k)
+      if (slot_site(c, k) >= 0) {
+        const size_t row = (size_t)k*n_br + bi;
+        std::memcpy(dst, &hj[row*HALO_K], hc[row]*sizeof(double)); dst += hc[row];
+      }
+    if (own[bi])
+      EPV_CUDA(c, cudaMemcpyAsync(dst, c->d_jmp[c->cur] + c->h_jbase[bi], own[bi]*sizeof(double),
+                                  cudaMemcpyDeviceToHost, c->stream));
+    dst += own[bi];
+    for (int k = HALO_W; k < 2*HALO_W; ++k)
+      if (slot_site(c, k) >= 0) {
+        const size_t row = (size_t)k*n_br + bi;
+        std::memcpy(dst, &hj[row*HALO_K], hc[row]*sizeof(double)); dst += hc[row];
+      }
+  }
   EPV_CUDA(c, cudaStreamSynchronize(c->stream));
-  cudaFree(t_init); cudaFree(t_off); cudaFree(t_pre);
   for (int b = 0; b < c->n_nodes; ++b) tot_time[b] = c->h_branch[b];
   EPV_CUDA(c, cudaGetLastError());
   return 0;

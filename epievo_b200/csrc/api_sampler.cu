@@ -220,9 +220,9 @@ int epv_scale_jump_times(epv_ctx *c, const double *new_branches) {
   }
   double *d_scale = reinterpret_cast<double *>(c->d_mail);
   EPV_CUDA(c, cudaMemcpyAsync(d_scale, scale.data(), c->n_nodes*sizeof(double), cudaMemcpyHostToDevice, c->stream));
-  launch_scale_jumps(c->d_jmp[c->cur], c->d_jbase, c->d_off[c->cur], c->off_pitch, c->n_sites,
-                     c->n_nodes - 1, d_scale, c->stream);
-  ++c->launches;
+  launch_scale_jumps(c->d_jmp[c->cur], c->d_jbase, c->d_off[c->cur], c->off_pitch, c->n_own(),
+                     c->n_nodes - 1, d_scale, c->d_hjmp, c->stream);
+  c->launches += 2;
   for (int b = 1; b < c->n_nodes; ++b) c->h_branch[b] = new_branches[b];
   EPV_CUDA(c, cudaMemcpyAsync(c->d_branch, c->h_branch.data(), c->n_nodes*sizeof(double), cudaMemcpyHostToDevice, c->stream));
   EPV_CUDA(c, cudaStreamSynchronize(c->stream));

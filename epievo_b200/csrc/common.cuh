@@ -15,6 +15,8 @@ enum : unsigned {
   ERR_SCRATCH_SIZE  = 4u,   // one proposal longer than a scratch slot
   ERR_SAMPLER_STUCK = 8u,   // end-conditioned sampler exceeded its iteration cap
   ERR_BAD_INPUT     = 16u,
+  ERR_HALO_CAPACITY = 32u,  // a boundary row has more than HALO_K jumps
+  ERR_HALO_MISMATCH = 64u,  // a halo record arrived for another site / colour
 };
 
 // ---- model constants, one copy in __constant__ memory per context upload ---------
@@ -29,11 +31,24 @@ struct ModelParams {
 //   off[bi*off_pitch + s]   uint32, s in [0, n_sites]   offsets into that branch's jumps
 //   jmp + jbase[bi]         double                       jump times, strictly inside (0, T_b)
 // Initial states are site-major bit sets: bit (node&7) of state[s*W + (node>>3)].
+// Only the OWNED sites [own_lo, own_hi) of the local index space live in the CSR (row
+// index = site - own_lo).  The <= 3 halo sites on either side (copies of the neighbour
+// GPUs' boundary sites, refreshed after every colour pass) are kept in a small
+// fixed-capacity halo store so that a refresh never forces a re-compaction:
+//   hcnt[slot*n_br + bi], hjmp[(slot*n_br + bi)*HALO_K ...], slot = site for the low
+//   halo, 3 + (site - own_hi) for the high halo.
+constexpr int HALO_W = 3;        // halo width in sites (dependence radius is 2)
+constexpr int HALO_K = 48;       // jump capacity of one halo row (overflow = loud error)
+
 struct PathView {
   const uint32_t *off;
   const double *jmp;
   const uint64_t *jbase;    // [n_branches] start of each branch's slice of jmp
   uint64_t off_pitch;
+  uint64_t own_lo, own_hi;
+  const uint16_t *hcnt;
+  const double *hjmp;
+  int n_br;
 };
 
 struct TreeDev {

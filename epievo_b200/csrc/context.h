@@ -33,6 +33,8 @@ struct epv_ctx {
   uint64_t jmp_total_cap = 0;
   int cur = 0;
   uint8_t *d_state = nullptr;
+  uint8_t *d_stage_init = nullptr;           // staging of the host exchange format
+  unsigned long long *d_stage_off = nullptr;
   double *d_tri = nullptr;
   bool tri_valid = false;
 
@@ -54,9 +56,9 @@ struct epv_ctx {
   unsigned long long *h_mail = nullptr;      // [64 + n_nodes]
   unsigned long long *d_mail = nullptr;
 
-  // halo blobs
-  void *d_halo[4] = {nullptr, nullptr, nullptr, nullptr};
-  uint64_t halo_bytes[4] = {0, 0, 0, 0};
+  // halo store (rows of the <= 3 + 3 halo sites, outside the CSR; see common.cuh)
+  uint16_t *d_hcnt = nullptr;               // [2*HALO_W][n_br]
+  double *d_hjmp = nullptr;                 // [2*HALO_W][n_br][HALO_K]
 
   // instrumentation
   uint64_t launches = 0, mh_launches = 0;
@@ -71,12 +73,14 @@ struct epv_ctx {
 
   epv::PathView view(int which) const {
     epv::PathView v; v.off = d_off[which]; v.jmp = d_jmp[which]; v.jbase = d_jbase;
-    v.off_pitch = off_pitch; return v;
+    v.off_pitch = off_pitch; v.own_lo = halo_lo; v.own_hi = n_sites - halo_hi;
+    v.hcnt = d_hcnt; v.hjmp = d_hjmp; v.n_br = n_nodes - 1; return v;
   }
   epv::TreeDev tree() const {
     epv::TreeDev t; t.n_nodes = n_nodes; t.parent = d_parent; t.subtree = d_subtree;
     t.branch = d_branch; return t;
   }
+  uint64_t n_own() const { return n_sites - halo_lo - halo_hi; }
   uint64_t upd_lo() const { return halo_lo; }
   uint64_t upd_hi() const { return n_sites - halo_hi; }
   int64_t global0() const { return (int64_t)site_begin - (int64_t)halo_lo; }

@@ -69,15 +69,35 @@ void launch_axpy_stats(double *J_sum, double *D_sum, const double *J, const doub
                        cudaStream_t st);
 
 void launch_scale_jumps(double *jmp, const uint64_t *jbase, const uint32_t *off,
-                        uint64_t off_pitch, uint64_t n_sites, int n_branches,
-                        const double *scale, cudaStream_t st);
+                        uint64_t off_pitch, uint64_t n_own, int n_branches,
+                        const double *scale, double *hjmp, cudaStream_t st);
 
 // host exchange format <-> device layout
 void launch_import(const uint8_t *h_init, const unsigned long long *h_off,
-                   uint64_t n_sites, int n_nodes, uint32_t *off, uint64_t off_pitch,
-                   uint8_t *state, int W, cudaStream_t st);
-void launch_export(const uint32_t *off, uint64_t off_pitch, const uint8_t *state, int W,
-                   uint64_t n_sites, int n_nodes, const uint64_t *jprefix,
-                   uint8_t *h_init, unsigned long long *h_off, cudaStream_t st);
+                   uint64_t n_sites, int n_nodes, uint64_t own_lo, uint64_t n_own,
+                   uint32_t *off, uint64_t off_pitch, uint8_t *state, int W, cudaStream_t st);
+void launch_export(const PathView &pv, const uint8_t *state, int W, uint64_t n_sites,
+                   int n_nodes, const uint64_t *jprefix, uint8_t *h_init,
+                   unsigned long long *h_off, cudaStream_t st);
+
+// ---- halo exchange (multi-GPU): one boundary site per side per colour pass -------------
+// Record (8-byte words): [0..2] tri_llh[s-1], [s], [s+1]; [3] global site index;
+// [4 .. 4+SW) state bytes; then n_br u16 jump counts packed in CW words; then
+// n_br*HALO_K jump times.
+struct HaloArgs {
+  PathView pv;
+  uint8_t *state; int W;
+  double *tri_llh;
+  uint64_t n_sites; int64_t global0;
+  uint16_t *hcnt; double *hjmp;        // writable halo store (unpack)
+  unsigned *err;
+};
+size_t halo_record_words(int n_nodes);
+// site_lo / site_hi: local index of the owned boundary site to pack (or -1: side absent)
+void launch_halo_pack(const HaloArgs &a, int64_t site_lo, unsigned long long *rec_lo,
+                      int64_t site_hi, unsigned long long *rec_hi, cudaStream_t st);
+// site_lo / site_hi: local index of the halo site each record must describe (or -1)
+void launch_halo_unpack(const HaloArgs &a, int64_t site_lo, const unsigned long long *rec_lo,
+                        int64_t site_hi, const unsigned long long *rec_hi, cudaStream_t st);
 
 }  // namespace epv

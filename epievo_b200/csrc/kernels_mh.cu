@@ -111,14 +111,19 @@ mh_pass_kernel(const PassArgs a) {
   const unsigned acc_mask = __ballot_sync(0xffffffffu, accepted);
   if (lane == 0 && acc_mask) atomicAdd(a.n_accept, (unsigned long long)__popc(acc_mask));
 
-  // ---- phase 2: new row lengths, summed per thread ------------------------------
+  // ---- phase 2: new row lengths of the group's OWNED sites, summed per thread -----
+  // CSR row index of local site s is s - own_lo; the group's owned sites are the
+  // contiguous range [r0, r1) of it (empty for a group that lies in a halo).
+  const uint64_t own_lo = a.in.own_lo, own_hi = a.in.own_hi, n_own = own_hi - own_lo;
+  const uint64_t g_lo = max(s0, own_lo), g_hi = min(s0 + 3, own_hi);
+  const bool has_rows = g_lo < g_hi;
+  const uint64_t r0 = has_rows ? g_lo - own_lo : 0, r1 = has_rows ? g_hi - own_lo : 0;
   for (int bi = 0; bi < n_br; ++bi) {
     uint32_t sum = 0;
-    if (s0 < a.n_sites) {
+    if (has_rows) {
       const uint32_t *o = a.in.off + (uint64_t)bi*a.in.off_pitch;
-      const uint64_t hi = min(s0 + 3, a.n_sites);
-      sum = o[hi] - o[s0];
-      if (accepted) sum = sum - (o[st + 1] - o[st]) + pn[bi + 1];
+      sum = o[r1] - o[r0];
+      if (accepted) sum = sum - (o[st - own_lo + 1] - o[st - own_lo]) + pn[bi + 1];
     }
     s_len[bi*MH_THREADS + t] = sum;
   }
@@ -146,10 +151,10 @@ mh_pass_kernel(const PassArgs a) {
 #pragma unroll
     for (int k = 0; k < MH_THREADS/32; ++k) { row[lane*(MH_THREADS/32) + k] = run; run += v[k]; }
     if (tile == a.n_tiles - 1 && lane == 31)
-      a.off_out[(uint64_t)bi*a.in.off_pitch + a.n_sites] = base + tot;
+      a.off_out[(uint64_t)bi*a.in.off_pitch + n_own] = base + tot;
   }
   __syncthreads();
-  if (s_fail || s0 >= a.n_sites) return;
+  if (s_fail || !has_rows) return;
 
   // ---- phase 4: write the rebuilt rows ---------------------------------------------
   int poff = 0;
@@ -159,16 +164,15 @@ mh_pass_kernel(const PassArgs a) {
     const double *src_base = a.in.jmp + a.in.jbase[bi];
     double *dst_base = a.jmp_out + a.in.jbase[bi];
     uint32_t w = s_len[bi*MH_THREADS + t];
-    const uint64_t hi = min(s0 + 3, a.n_sites);
-    for (uint64_t s = s0; s < hi; ++s) {
-      oo[s] = w;
-      if (accepted && s == st) {
+    for (uint64_t r = r0; r < r1; ++r) {
+      oo[r] = w;
+      if (accepted && r + own_lo == st) {
         const int n = pn[bi + 1];
         for (int k = 0; k < n; ++k) dst_base[w + k] = pr.pj[poff + k];
         w += n;
       }
       else {
-        const uint32_t b = o[s], e = o[s + 1];
+        const uint32_t b = o[r], e = o[r + 1];
         for (uint32_t k = b; k < e; ++k) dst_base[w + (k - b)] = src_base[k];
         w += e - b;
       }

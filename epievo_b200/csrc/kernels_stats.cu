@@ -136,15 +136,19 @@ scale_kernel(double *jmp, const uint64_t *jbase, const uint32_t *off, uint64_t p
     p[k] *= sc;
 }
 
+// Host exchange format (node-major, all local sites) -> device layout: CSR offsets of
+// the owned sites [own_lo, own_lo + n_own], state bit sets of every local site.
 __global__ void __launch_bounds__(256)
 import_kernel(const uint8_t *h_init, const unsigned long long *h_off, uint64_t n_sites,
-              int n_nodes, uint32_t *off, uint64_t pitch, uint8_t *state, int W) {
+              int n_nodes, uint64_t own_lo, uint64_t n_own, uint32_t *off, uint64_t pitch,
+              uint8_t *state, int W) {
   const uint64_t s = (uint64_t)blockIdx.x*blockDim.x + threadIdx.x;
-  if (s > n_sites) return;
-  for (int b = 1; b < n_nodes; ++b)
-    off[(uint64_t)(b - 1)*pitch + s] =
-      (uint32_t)(h_off[(uint64_t)b*n_sites + s] - h_off[(uint64_t)b*n_sites]);
-  if (s == n_sites) return;
+  if (s <= n_own)
+    for (int b = 1; b < n_nodes; ++b) {
+      const unsigned long long *o = h_off + (uint64_t)b*n_sites + own_lo;
+      off[(uint64_t)(b - 1)*pitch + s] = (uint32_t)(o[s] - o[0]);
+    }
+  if (s >= n_sites) return;
   for (int w = 0; w < W; ++w) {
     unsigned bits = 0;
     for (int k = 0; k < 8; ++k) {
@@ -155,18 +159,41 @@ import_kernel(const uint8_t *h_init, const unsigned long long *h_off, uint64_t n
   }
 }
 
+// Device layout -> host exchange format.  jprefix[bi] = jumps held by branches < bi
+// (halo rows included); within a branch the order is halo-low rows, owned rows,
+// halo-high rows, i.e. site order.
 __global__ void __launch_bounds__(256)
-export_kernel(const uint32_t *off, uint64_t pitch, const uint8_t *state, int W,
-              uint64_t n_sites, int n_nodes, const uint64_t *jprefix, uint8_t *h_init,
-              unsigned long long *h_off) {
+export_kernel(const PathView pv, const uint8_t *state, int W, uint64_t n_sites, int n_nodes,
+              const uint64_t *jprefix, uint8_t *h_init, unsigned long long *h_off) {
   const uint64_t s = (uint64_t)blockIdx.x*blockDim.x + threadIdx.x;
   if (s >= n_sites) return;
   h_init[s] = 0; h_off[s] = 0;
+  const uint64_t n_own = pv.own_hi - pv.own_lo;
   for (int b = 1; b < n_nodes; ++b) {
+    const int bi = b - 1;
     h_init[(uint64_t)b*n_sites + s] = (uint8_t)state_bit(state, W, s, b);
-    h_off[(uint64_t)b*n_sites + s] = jprefix[b - 1] + off[(uint64_t)(b - 1)*pitch + s];
+    uint64_t lo_tot = 0, before = 0;
+    for (uint64_t k = 0; k < pv.own_lo; ++k) {
+      if (k < s) before += pv.hcnt[k*pv.n_br + bi];
+      lo_tot += pv.hcnt[k*pv.n_br + bi];
+    }
+    uint64_t o;
+    if (s < pv.own_lo) o = before;
+    else if (s < pv.own_hi) o = lo_tot + pv.off[(uint64_t)bi*pv.off_pitch + (s - pv.own_lo)];
+    else {
+      o = lo_tot + pv.off[(uint64_t)bi*pv.off_pitch + n_own];
+      for (uint64_t k = pv.own_hi; k < s; ++k) o += pv.hcnt[(HALO_W + (k - pv.own_hi))*pv.n_br + bi];
+    }
+    h_off[(uint64_t)b*n_sites + s] = jprefix[bi] + o;
   }
   if (s == 0) h_off[(uint64_t)n_nodes*n_sites] = jprefix[n_nodes - 1];
+}
+
+__global__ void
+scale_halo_kernel(double *hjmp, int n_br, const double *scale) {
+  const int row = blockIdx.x;                     // slot*n_br + bi
+  const double sc = scale[row % n_br + 1];
+  for (int k = threadIdx.x; k < HALO_K; k += blockDim.x) hjmp[(size_t)row*HALO_K + k] *= sc;
 }
 
 }  // namespace
@@ -207,25 +234,27 @@ launch_axpy_stats(double *Js, double *Ds, const double *J, const double *D, int 
 
 void
 launch_scale_jumps(double *jmp, const uint64_t *jbase, const uint32_t *off, uint64_t pitch,
-                   uint64_t n_sites, int n_branches, const double *scale, cudaStream_t st) {
+                   uint64_t n_own, int n_branches, const double *scale, double *hjmp,
+                   cudaStream_t st) {
   dim3 grid(592, n_branches);
-  scale_kernel<<<grid, 256, 0, st>>>(jmp, jbase, off, pitch, n_sites, scale);
+  scale_kernel<<<grid, 256, 0, st>>>(jmp, jbase, off, pitch, n_own, scale);
+  scale_halo_kernel<<<2*HALO_W*n_branches, 64, 0, st>>>(hjmp, n_branches, scale);
 }
 
 void
 launch_import(const uint8_t *h_init, const unsigned long long *h_off, uint64_t n_sites,
-              int n_nodes, uint32_t *off, uint64_t pitch, uint8_t *state, int W,
-              cudaStream_t st) {
-  import_kernel<<<(unsigned)((n_sites + 256)/256), 256, 0, st>>>(h_init, h_off, n_sites,
-                                                                 n_nodes, off, pitch, state, W);
+              int n_nodes, uint64_t own_lo, uint64_t n_own, uint32_t *off, uint64_t pitch,
+              uint8_t *state, int W, cudaStream_t st) {
+  import_kernel<<<(unsigned)((n_sites + 256)/256), 256, 0, st>>>(h_init, h_off, n_sites, n_nodes,
+                                                                 own_lo, n_own, off, pitch, state, W);
 }
 
 void
-launch_export(const uint32_t *off, uint64_t pitch, const uint8_t *state, int W,
-              uint64_t n_sites, int n_nodes, const uint64_t *jprefix, uint8_t *h_init,
-              unsigned long long *h_off, cudaStream_t st) {
-  export_kernel<<<(unsigned)((n_sites + 255)/256), 256, 0, st>>>(off, pitch, state, W, n_sites,
-                                                                 n_nodes, jprefix, h_init, h_off);
+launch_export(const PathView &pv, const uint8_t *state, int W, uint64_t n_sites, int n_nodes,
+              const uint64_t *jprefix, uint8_t *h_init, unsigned long long *h_off,
+              cudaStream_t st) {
+  export_kernel<<<(unsigned)((n_sites + 255)/256), 256, 0, st>>>(pv, state, W, n_sites, n_nodes,
+                                                                 jprefix, h_init, h_off);
 }
 
 }  // namespace epv

@@ -32,7 +32,7 @@ upward(const ModelParams &mp, const SiteCtx &c, double *q) {
   for (int v = 0; v < n_nodes; ++v) {
     double q0 = 1.0, q1 = 1.0;
     if (c.tree.subtree[v] == 1) {
-      const uint32_t *o = c.pv.off + (uint64_t)(v - 1)*c.pv.off_pitch + c.site;
+      const uint32_t *o = c.pv.off + (uint64_t)(v - 1)*c.pv.off_pitch + (c.site - c.pv.own_lo);
       const int leaf = state_bit(c.state, c.W, c.site, v) ^ ((o[1] - o[0]) & 1);
       q0 = leaf ? 0.0 : 1.0; q1 = leaf ? 1.0 : 0.0;
     }

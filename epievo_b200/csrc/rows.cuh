@@ -15,12 +15,19 @@ struct Row {
 
 __device__ __forceinline__ Row
 load_row(const PathView &pv, const uint8_t *state, int W, int bi, uint64_t site) {
-  const uint32_t *o = pv.off + (uint64_t)bi*pv.off_pitch + site;
-  const uint32_t a = o[0], b = o[1];
   Row r;
-  r.ptr = pv.jmp + pv.jbase[bi] + a;
-  r.n = (int)(b - a);
   r.init = state_bit(state, W, site, bi + 1);
+  if (site >= pv.own_lo && site < pv.own_hi) {
+    const uint32_t *o = pv.off + (uint64_t)bi*pv.off_pitch + (site - pv.own_lo);
+    const uint32_t a = o[0], b = o[1];
+    r.ptr = pv.jmp + pv.jbase[bi] + a;
+    r.n = (int)(b - a);
+  }
+  else {
+    const int slot = site < pv.own_lo ? (int)site : HALO_W + (int)(site - pv.own_hi);
+    r.n = pv.hcnt[slot*pv.n_br + bi];
+    r.ptr = pv.hjmp + (size_t)(slot*pv.n_br + bi)*HALO_K;
+  }
   return r;
 }
 

@@ -147,6 +147,18 @@ class Context:
                                            _d(D), C.byref(n)))
         return J.reshape(-1, 8), D.reshape(-1, 8), n.value
 
+    # -- multi-GPU halo exchange (device buffers given as raw addresses) ------------------
+    def halo_record_bytes(self) -> int:
+        n = C.c_uint64()
+        self._ck(self.lib.epv_halo_record_bytes(self.h, C.byref(n)))
+        return n.value
+
+    def halo_pack(self, colour: int, rec_lo_ptr: Optional[int], rec_hi_ptr: Optional[int]):
+        self._ck(self.lib.epv_halo_pack(self.h, colour, C.c_void_p(rec_lo_ptr), C.c_void_p(rec_hi_ptr)))
+
+    def halo_unpack(self, colour: int, rec_lo_ptr: Optional[int], rec_hi_ptr: Optional[int]):
+        self._ck(self.lib.epv_halo_unpack(self.h, colour, C.c_void_p(rec_lo_ptr), C.c_void_p(rec_hi_ptr)))
+
     # -- statistics -----------------------------------------------------------------
     def suffstats(self):
         J = np.zeros(self.n_nodes * 8)

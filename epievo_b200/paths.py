@@ -86,6 +86,23 @@ class PathSet:
                        else np.zeros(0), self.tot_time.copy(), list(self.node_names))
 
     @staticmethod
+    def concat_sites(parts: Sequence["PathSet"]) -> "PathSet":
+        """Concatenate PathSets along the site axis (same nodes / branch lengths)."""
+        n_nodes = parts[0].n_nodes
+        n = sum(p.n_sites for p in parts)
+        init = np.concatenate([p.init_state.reshape(n_nodes, -1) for p in parts], axis=1)
+        lens = np.concatenate([p.row_len() for p in parts], axis=1)
+        chunks = []
+        for b in range(n_nodes):
+            for p in parts:
+                chunks.append(p.jumps[int(p.row_off[b * p.n_sites]):int(p.row_off[(b + 1) * p.n_sites])])
+        off = np.zeros(n_nodes * n + 1, np.uint64)
+        np.cumsum(lens.reshape(-1), out=off[1:].view(np.int64))
+        return PathSet(n, n_nodes, init.reshape(-1), off,
+                       np.concatenate(chunks) if chunks else np.zeros(0),
+                       parts[0].tot_time.copy(), list(parts[0].node_names))
+
+    @staticmethod
     def from_rows(n_sites: int, n_nodes: int, init_state, rows, tot_time,
                   node_names: Sequence[str] = ()) -> "PathSet":
         """rows[node][site] is a sequence of jump times (node 0 may be empty/None)."""

@@ -1,0 +1,165 @@
+"""Multi-GPU driver: contiguous site blocks, one per GPU, 3-site halos, one tiny
+neighbour exchange per colour pass and one all-reduce of the J/D sums per E-step
+(SURVEY 8e).  The transport is pluggable so the same protocol code runs
+
+* across processes with torch.distributed (NCCL on device buffers; one rank per GPU), and
+* inside one process over several contexts (``LocalExchange``: device-to-device copies),
+  which is how the protocol is tested on a single GPU.
+
+Determinism: the Philox streams are keyed by the GLOBAL site index, so a sharded run
+reproduces the single-GPU run bit for bit (tests/test_gpu_sharded.py).
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from .paths import PathSet
+
+HALO = 3
+
+
+def partition(n_global: int, world: int) -> List[Tuple[int, int]]:
+    """Contiguous blocks whose starts are multiples of 3 (colour alignment)."""
+    n3 = n_global // 3
+    cuts = [3 * ((n3 * r) // world) for r in range(world)] + [n_global]
+    blocks = [(cuts[r], cuts[r + 1]) for r in range(world)]
+    for lo, hi in blocks:
+        if hi - lo < 2 * HALO:
+            raise ValueError("too few sites for %d shards" % world)
+    return blocks
+
+
+def shard_bounds(n_global: int, world: int, rank: int) -> Tuple[int, int, int, int]:
+    lo, hi = partition(n_global, world)[rank]
+    return lo, hi, (HALO if rank > 0 else 0), (HALO if rank + 1 < world else 0)
+
+
+def local_paths(ps: PathSet, n_global: int, world: int, rank: int) -> PathSet:
+    lo, hi, hl, hh = shard_bounds(n_global, world, rank)
+    return ps.site_slice(lo - hl, hi + hh)
+
+
+class Shard:
+    """One context + its four device-side halo records."""
+
+    def __init__(self, ctx, n_global: int, world: int, rank: int, torch_device):
+        import torch
+        self.ctx, self.rank, self.world, self.n_global = ctx, rank, world, n_global
+        self.lo, self.hi, self.halo_lo, self.halo_hi = shard_bounds(n_global, world, rank)
+        ctx.set_shard(n_global, self.lo, self.hi, self.halo_lo, self.halo_hi)
+        nb = ctx.halo_record_bytes()
+        mk = lambda: torch.zeros(nb, dtype=torch.uint8, device=torch_device)
+        self.send_lo, self.send_hi, self.recv_lo, self.recv_hi = mk(), mk(), mk(), mk()
+
+    def _p(self, t, present):
+        return t.data_ptr() if present else None
+
+    def pack(self, colour):
+        self.ctx.halo_pack(colour, self._p(self.send_lo, self.halo_lo), self._p(self.send_hi, self.halo_hi))
+
+    def unpack(self, colour):
+        self.ctx.halo_unpack(colour, self._p(self.recv_lo, self.halo_lo), self._p(self.recv_hi, self.halo_hi))
+
+
+class DistExchange:
+    """torch.distributed transport: rank r talks to r-1 and r+1 only."""
+
+    def __init__(self, shard: Shard):
+        self.s = shard
+
+    def exchange(self):
+        import torch.distributed as dist
+        s, ops = self.s, []
+        if s.halo_lo:
+            ops += [dist.P2POp(dist.isend, s.send_lo, s.rank - 1), dist.P2POp(dist.irecv, s.recv_lo, s.rank - 1)]
+        if s.halo_hi:
+            ops += [dist.P2POp(dist.isend, s.send_hi, s.rank + 1), dist.P2POp(dist.irecv, s.recv_hi, s.rank + 1)]
+        if ops:
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+
+    def allreduce_sum(self, arr: np.ndarray) -> np.ndarray:
+        import torch
+        import torch.distributed as dist
+        t = torch.from_numpy(np.ascontiguousarray(arr, np.float64)).to(self.s.send_lo.device)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return t.cpu().numpy()
+
+
+class LocalExchange:
+    """All shards in one process: neighbour records move by device-to-device copy."""
+
+    def __init__(self, shards: Sequence[Shard]):
+        self.shards = list(shards)
+
+    def exchange(self):
+        for a, b in zip(self.shards[:-1], self.shards[1:]):
+            b.recv_lo.copy_(a.send_hi)
+            a.recv_hi.copy_(b.send_lo)
+
+
+def colour_pass(shards: Sequence[Shard], transport, colour: int, seed: int, sweep: int):
+    for s in shards:
+        s.ctx.colour_pass(colour, seed, sweep)
+        s.pack(colour)
+    transport.exchange()
+    for s in shards:
+        s.unpack(colour)
+
+
+def sweep(shards: Sequence[Shard], transport, seed: int, sweep_idx: int):
+    """SingleSiteSampler::single_iteration over all shards (3 colour passes)."""
+    for colour in range(3):
+        colour_pass(shards, transport, colour, seed, sweep_idx)
+
+
+def run_mcmc(shards: Sequence[Shard], transport, burn_in: int, batch: int, seed: int,
+             first_sweep: int = 0, allreduce=None):
+    """SingleSiteSampler::run_mcmc (reference SingleSiteSampler.cpp:550-598) over shards.
+    Returns batch-averaged J, D [n_nodes, 8] and the acceptance rate over all sites."""
+    sw = first_sweep
+    for _ in range(burn_in):
+        sweep(shards, transport, seed, sw)
+        sw += 1
+    for s in shards:
+        s.ctx.accept_count(reset=True)
+    n_nodes = shards[0].ctx.n_nodes
+    Js, Ds = np.zeros((n_nodes, 8)), np.zeros((n_nodes, 8))
+    for _ in range(batch):
+        sweep(shards, transport, seed, sw)
+        sw += 1
+        for s in shards:
+            J, D = s.ctx.suffstats()
+            Js += J
+            Ds += D
+    acc = float(sum(s.ctx.accept_count(reset=True) for s in shards))
+    flat = np.concatenate([Js.ravel(), Ds.ravel(), [acc]])
+    if allreduce is not None:
+        flat = allreduce(flat)
+    k = n_nodes * 8
+    n_global = shards[0].n_global
+    return (flat[:k].reshape(n_nodes, 8) / batch, flat[k:2 * k].reshape(n_nodes, 8) / batch,
+            flat[-1] / (batch * (n_global - 2)))
+
+
+def gather_paths(parts: Sequence[PathSet], n_global: int, world: int) -> PathSet:
+    """Owned blocks of every shard's local PathSet (halo stripped) -> one PathSet."""
+    n_nodes = parts[0].n_nodes
+    init = np.zeros((n_nodes, n_global), np.uint8)
+    lens = np.zeros((n_nodes, n_global), np.int64)
+    chunks = [[] for _ in range(n_nodes)]
+    for r, ps in enumerate(parts):
+        lo, hi, hl, hh = shard_bounds(n_global, world, r)
+        own = ps.site_slice(hl, hl + (hi - lo))
+        init[:, lo:hi] = own.init_state.reshape(n_nodes, -1)
+        lens[:, lo:hi] = own.row_len()
+        for b in range(n_nodes):
+            a, e = int(own.row_off[b * own.n_sites]), int(own.row_off[(b + 1) * own.n_sites])
+            chunks[b].append(own.jumps[a:e])
+    off = np.zeros(n_nodes * n_global + 1, np.uint64)
+    np.cumsum(lens.reshape(-1), out=off[1:].view(np.int64))
+    jumps = np.concatenate([np.concatenate(c) for c in chunks]) if n_nodes else np.zeros(0)
+    return PathSet(n_global, n_nodes, init.reshape(-1), off, jumps, parts[0].tot_time.copy(),
+                   list(parts[0].node_names))

@@ -60,7 +60,8 @@ int epv_set_model(epv_ctx *ctx, const double *triplet_rates, const double *T);
 /* Sharding (one context per GPU): this context holds global sites
  * [site_begin - halo_lo, site_end + halo_hi) of an n_global-site problem; only sites
  * in [site_begin, site_end) are updated / counted here.  site_begin must be a
- * multiple of 3.  Default (never called): the whole problem, no halo. */
+ * multiple of 3; halo_lo / halo_hi are 3 on a side with a neighbour, 0 at a global
+ * end; a shard owns at least 6 sites.  Default (never called): the whole problem. */
 int epv_set_shard(epv_ctx *ctx, uint64_t n_global, uint64_t site_begin,
                   uint64_t site_end, uint64_t halo_lo, uint64_t halo_hi);
 
@@ -116,6 +117,19 @@ int epv_scale_jump_times(epv_ctx *ctx, const double *new_branches);
 int epv_pass(epv_ctx *ctx, int colour, uint64_t seed, uint64_t sweep_idx);
 /* Accept counter of the passes issued since the last call with reset != 0. */
 int epv_accept_count(epv_ctx *ctx, int reset, uint64_t *n_accepted);
+
+/* Halo exchange.  After colour pass c, exactly one of the three boundary sites on each
+ * side of a shard can have changed (radius-2 dependence, stride-3 colours).
+ * epv_halo_pack writes that site's record -- rows of every branch, state bits, the three
+ * tri_llh entries its update wrote, its global index -- to the DEVICE buffers rec_lo
+ * (for the lower-index neighbour) and rec_hi (for the higher-index neighbour), each
+ * epv_halo_record_bytes long; the driver moves them to the neighbours (NCCL send/recv or
+ * a peer copy) and calls epv_halo_unpack with the records received FROM the lower
+ * (rec_lo) and higher (rec_hi) neighbour.  Pass NULL for a side that has no neighbour.
+ * All work is enqueued on the context's stream. */
+int epv_halo_record_bytes(epv_ctx *ctx, uint64_t *bytes);
+int epv_halo_pack(epv_ctx *ctx, int colour, void *rec_lo, void *rec_hi);
+int epv_halo_unpack(epv_ctx *ctx, int colour, const void *rec_lo, const void *rec_hi);
 
 /* ---- deterministic per-site intermediates (parity tests of a2/a3/a4/a7) --------- */
 /* For local site `site`: the neighbour-interval lists of every node
