@@ -1,0 +1,179 @@
+/* SingleSiteSampler_b200.cpp -- the reference's SingleSiteSampler interface
+ * (src/libepievo/SingleSiteSampler.hpp:35-81) implemented over the C-ABI of
+ * libepievo_b200.so.  Host glue only: flatten vector<vector<Path>> [site][node] into the
+ * node-major CSR exchange format, call the device path, unflatten. */
+#include "SingleSiteSampler.hpp"
+
+#include <cstdlib>
+#include <stdexcept>
+#include <string>
+
+#include "epievo_b200.h"
+
+using std::vector;
+
+static int
+device_from_env() {
+  const char *e = std::getenv("EPIEVO_B200_DEVICE");
+  return e ? std::atoi(e) : 0;
+}
+
+static epv_ctx *
+new_context() {
+  epv_ctx *c = nullptr;
+  if (epv_create(&c, device_from_env()) != 0 || !c)
+    throw std::runtime_error("epievo_b200: no usable CUDA device (there is no CPU fallback)");
+  return c;
+}
+
+SingleSiteSampler::SingleSiteSampler(const size_t n_burn_in, const size_t n_batch) :
+  SAMPLE_ROOT(false), burn_in(n_burn_in), batch(n_batch), ctx(new_context()),
+  sweep_counter(0) {}
+
+SingleSiteSampler::~SingleSiteSampler() { epv_destroy(ctx); }
+
+void
+SingleSiteSampler::check(int rc) const {
+  if (rc != 0) throw std::runtime_error(std::string("epievo_b200: ") + epv_last_error(ctx));
+}
+
+void
+SingleSiteSampler::configure(const EpiEvoModel &the_model, const TreeHelper &th) {
+  vector<uint64_t> ss(th.subtree_sizes.begin(), th.subtree_sizes.end());
+  vector<uint64_t> pi(th.parent_ids.begin(), th.parent_ids.end());
+  check(epv_set_tree(ctx, th.n_nodes, ss.data(), pi.data(), th.branches.data()));
+  const double T[4] = {the_model.T(0, 0), the_model.T(0, 1), the_model.T(1, 0), the_model.T(1, 1)};
+  check(epv_set_model(ctx, the_model.triplet_rates.data(), T));
+}
+
+/* [site][node] -> node-major CSR (the order of the local-paths file, Path.cpp:123-148) */
+void
+SingleSiteSampler::upload(const vector<vector<Path> > &paths, const TreeHelper &th) {
+  const size_t n_sites = paths.size(), n_nodes = th.n_nodes;
+  init_state.assign(n_sites*n_nodes, 0);
+  row_off.assign(n_sites*n_nodes + 1, 0);
+  tot_time.assign(n_nodes, 0.0);
+  size_t total = 0;
+  for (size_t b = 1; b < n_nodes; ++b)
+    for (size_t s = 0; s < n_sites; ++s) total += paths[s][b].jumps.size();
+  jumps.resize(total ? total : 1);
+  size_t k = 0;
+  for (size_t s = 0; s < n_sites; ++s) row_off[s] = 0;
+  for (size_t b = 1; b < n_nodes; ++b) {
+    tot_time[b] = paths[0][b].tot_time;
+    for (size_t s = 0; s < n_sites; ++s) {
+      const Path &p = paths[s][b];
+      const size_t r = b*n_sites + s;
+      init_state[r] = p.init_state;
+      row_off[r] = k;
+      for (size_t j = 0; j < p.jumps.size(); ++j) jumps[k++] = p.jumps[j];
+    }
+  }
+  row_off[n_sites*n_nodes] = k;
+  check(epv_upload_paths(ctx, n_sites, n_nodes, init_state.data(),
+                         reinterpret_cast<const uint64_t *>(row_off.data()), jumps.data(),
+                         tot_time.data()));
+}
+
+void
+SingleSiteSampler::download(vector<vector<Path> > &paths) {
+  uint64_t n_sites = 0, n_nodes = 0, n_jumps = 0;
+  check(epv_paths_size(ctx, &n_sites, &n_nodes, &n_jumps));
+  jumps.resize(n_jumps ? n_jumps : 1);
+  check(epv_download_paths(ctx, init_state.data(), reinterpret_cast<uint64_t *>(row_off.data()),
+                           jumps.data(), tot_time.data()));
+  for (size_t b = 1; b < n_nodes; ++b)
+    for (size_t s = 0; s < n_sites; ++s) {
+      const size_t r = b*n_sites + s;
+      Path &p = paths[s][b];
+      p.init_state = init_state[r] != 0;
+      p.tot_time = tot_time[b];
+      p.jumps.assign(jumps.begin() + row_off[r], jumps.begin() + row_off[r + 1]);
+    }
+}
+
+/* The reference caches tri_llh here (SingleSiteSampler.cpp:449-475).  The device cache
+ * is rebuilt whenever model, tree or paths change, so nothing is left to do. */
+void
+SingleSiteSampler::reset(const EpiEvoModel &, vector<vector<Path> > &) {}
+
+static uint64_t
+seed_from(std::mt19937 &gen) {
+  const uint64_t hi = gen(), lo = gen();
+  return (hi << 32) | lo;
+}
+
+bool
+SingleSiteSampler::Metropolis_Hastings_site(const EpiEvoModel &the_model, const TreeHelper &th,
+                                            const size_t site_id,
+                                            vector<vector<Path> > &paths, std::mt19937 &gen) {
+  if (site_id != 1) return true;      // see the header: one sweep per caller loop
+  configure(the_model, th);
+  upload(paths, th);
+  uint64_t n_acc = 0;
+  check(epv_sweep(ctx, seed_from(gen), sweep_counter++, &n_acc));
+  download(paths);
+  return n_acc > 0;
+}
+
+void
+SingleSiteSampler::run_mcmc(const EpiEvoModel &the_model, const TreeHelper &th,
+                            vector<vector<Path> > &paths, std::mt19937 &gen,
+                            vector<vector<double> > &J_all_sites,
+                            vector<vector<double> > &D_all_sites, double &acceptance_rate) {
+  configure(the_model, th);
+  upload(paths, th);
+  vector<double> J(th.n_nodes*8), D(th.n_nodes*8);
+  check(epv_run_mcmc(ctx, burn_in, batch, seed_from(gen), sweep_counter, J.data(), D.data(),
+                     &acceptance_rate));
+  sweep_counter += burn_in + batch;
+  download(paths);
+  J_all_sites.assign(th.n_nodes, vector<double>(8, 0.0));   // row 0 unused, as the reference
+  D_all_sites.assign(th.n_nodes, vector<double>(8, 0.0));
+  for (size_t b = 1; b < th.n_nodes; ++b)
+    for (size_t t = 0; t < 8; ++t) {
+      J_all_sites[b][t] = J[b*8 + t];
+      D_all_sites[b][t] = D[b*8 + t];
+    }
+}
+
+namespace epievo_b200 {
+
+/* get_sufficient_statistics per branch (ParamEstimation.cpp:92-114) on the GPU. */
+void
+get_sufficient_statistics(const vector<vector<Path> > &all_paths, const TreeHelper &th,
+                          vector<vector<double> > &J, vector<vector<double> > &D) {
+  // a throw-away context: tree + paths only (no model needed for J/D)
+  epv_ctx *c = nullptr;
+  if (epv_create(&c, device_from_env()) != 0 || !c)
+    throw std::runtime_error("epievo_b200: no usable CUDA device (there is no CPU fallback)");
+  struct Guard { epv_ctx *c; ~Guard() { epv_destroy(c); } } guard{c};
+  auto ck = [&](int rc) { if (rc) throw std::runtime_error(std::string("epievo_b200: ") + epv_last_error(c)); };
+  const size_t n_sites = all_paths.size(), n_nodes = th.n_nodes;
+  vector<uint64_t> ss(th.subtree_sizes.begin(), th.subtree_sizes.end());
+  vector<uint64_t> pi(th.parent_ids.begin(), th.parent_ids.end());
+  vector<double> br(n_nodes, 0.0);
+  for (size_t b = 1; b < n_nodes; ++b) br[b] = all_paths[0][b].tot_time;   // rows carry the time
+  ck(epv_set_tree(c, n_nodes, ss.data(), pi.data(), br.data()));
+  vector<unsigned char> init(n_sites*n_nodes, 0);
+  vector<uint64_t> off(n_sites*n_nodes + 1, 0);
+  vector<double> jmp;
+  for (size_t b = 1; b < n_nodes; ++b)
+    for (size_t s2 = 0; s2 < n_sites; ++s2) {
+      const Path &p = all_paths[s2][b];
+      init[b*n_sites + s2] = p.init_state;
+      off[b*n_sites + s2] = jmp.size();
+      jmp.insert(jmp.end(), p.jumps.begin(), p.jumps.end());
+    }
+  off[n_sites*n_nodes] = jmp.size();
+  if (jmp.empty()) jmp.push_back(0.0);
+  ck(epv_upload_paths(c, n_sites, n_nodes, init.data(), off.data(), jmp.data(), br.data()));
+  vector<double> Jf(n_nodes*8), Df(n_nodes*8);
+  ck(epv_suffstats(c, Jf.data(), Df.data()));
+  J.assign(n_nodes, vector<double>(8, 0.0));
+  D.assign(n_nodes, vector<double>(8, 0.0));
+  for (size_t b = 1; b < n_nodes; ++b)
+    for (size_t t = 0; t < 8; ++t) { J[b][t] = Jf[b*8 + t]; D[b][t] = Df[b*8 + t]; }
+}
+
+}  // namespace epievo_b200

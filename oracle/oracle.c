@@ -306,6 +306,14 @@ orc_load_paths(uint64_t n_sites, uint64_t n_nodes, const uint8_t *init_state,
     }
 }
 
+/* overwrite one row in place (halo refresh in the sharding-protocol tests) */
+void
+orc_set_row(uint64_t site, uint64_t node, int init_state, uint64_t n, const double *jumps) {
+  path_t *p = &PATH(site, node);
+  p->init_state = init_state != 0;
+  dvec_assign(&p->jumps, jumps, n);
+}
+
 uint64_t
 orc_total_jumps(void) {
   uint64_t n = 0;
@@ -724,24 +732,60 @@ sampler_free(void) {
   g_S_live = 0;
 }
 
+static void
+sampler_init(uint64_t n_nodes, const double *rates, const double *T) {  /* reset :449-475 */
+  sampler_free();
+  memset(&g_S, 0, sizeof g_S);
+  g_S.n_nodes = n_nodes;
+  g_S.proposed = (path_t *)calloc(n_nodes, sizeof(path_t));
+  g_S.seg = (segvec *)calloc(n_nodes, sizeof(segvec));
+  g_S.fh = (fels_t *)calloc(n_nodes, sizeof(fels_t));
+  g_S.tri_llh = (double *)calloc(g_n_sites, sizeof(double));
+  for (size_t i = 0; i < N_TRIPLES; ++i) g_S.log_rates[i] = log(rates[i]);
+  orc_tri_llh(rates, T, g_S.tri_llh);
+  g_S_live = 1;
+}
+
+/* ---- colour-class sweeps with per-site reseeding (TEST INFRASTRUCTURE for the
+ * sharding protocol; not a reference function).  Each update of global site g in sweep
+ * k draws from mt19937 reseeded with a hash of (seed, k, g), so the result of a colour
+ * pass does not depend on how the sites are partitioned into shards -- the property the
+ * GPU path gets from its (seed, sweep, site)-keyed Philox streams. */
+void
+orc_sampler_init(uint64_t n_nodes, const uint64_t *subtree_sizes,
+                 const uint64_t *parent_ids, const double *branches,
+                 const double *rates, const double *T) {
+  sampler_init(n_nodes, rates, T);
+  g_S.subtree_sizes = subtree_sizes; g_S.parent_ids = parent_ids;
+  g_S.branches = branches; g_S.rates = rates; g_S.T = T;
+}
+
+uint64_t
+orc_colour_pass(int colour, uint64_t seed, uint64_t sweep, int64_t global0,
+                uint64_t n_global, uint64_t lo, uint64_t hi) {
+  uint64_t n_accepted = 0;
+  for (uint64_t s = lo; s < hi; ++s) {
+    const int64_t g = global0 + (int64_t)s;
+    if ((int)(s % 3) != colour || g < 1 || g + 1 >= (int64_t)n_global) continue;
+    uint64_t h = seed*0x9E3779B97F4A7C15ull + sweep;
+    h ^= h >> 29; h *= 0xBF58476D1CE4E5B9ull; h += (uint64_t)g;
+    h ^= h >> 32; h *= 0x94D049BB133111EBull; h ^= h >> 29;
+    orc_seed(h & 0xffffffffu);
+    n_accepted += (uint64_t)metropolis_hastings_site(&g_S, s);
+  }
+  return n_accepted;
+}
+
+void orc_get_tri_cache(double *out) { memcpy(out, g_S.tri_llh, g_n_sites*sizeof(double)); }
+void orc_set_tri_cache(uint64_t site, double v) { g_S.tri_llh[site] = v; }
+
 double
 orc_run_mcmc(uint64_t n_nodes, const uint64_t *subtree_sizes,
              const uint64_t *parent_ids, const double *branches,
              const double *rates, const double *T,
              uint64_t burn_in, uint64_t batch, int do_reset,
              double *J, double *D, double *acc_rate, double *seconds) {
-  if (!g_S_live || do_reset) {                               /* reset :449-475 */
-    sampler_free();
-    memset(&g_S, 0, sizeof g_S);
-    g_S.n_nodes = n_nodes;
-    g_S.proposed = (path_t *)calloc(n_nodes, sizeof(path_t));
-    g_S.seg = (segvec *)calloc(n_nodes, sizeof(segvec));
-    g_S.fh = (fels_t *)calloc(n_nodes, sizeof(fels_t));
-    g_S.tri_llh = (double *)calloc(g_n_sites, sizeof(double));
-    for (size_t i = 0; i < N_TRIPLES; ++i) g_S.log_rates[i] = log(rates[i]);
-    orc_tri_llh(rates, T, g_S.tri_llh);
-    g_S_live = 1;
-  }
+  if (!g_S_live || do_reset) sampler_init(n_nodes, rates, T);
   g_S.subtree_sizes = subtree_sizes; g_S.parent_ids = parent_ids;
   g_S.branches = branches; g_S.rates = rates; g_S.T = T;
 

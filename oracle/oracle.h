@@ -71,6 +71,16 @@ double orc_run_mcmc(uint64_t n_nodes, const uint64_t *subtree_sizes,
                     const double *rates, const double *T,
                     uint64_t burn_in, uint64_t batch, int do_reset,
                     double *J, double *D, double *acc_rate, double *seconds);
+/* sharding-protocol test support (not reference functions): colour-class sweeps with
+ * per-site reseeded mt19937, see oracle.c */
+void orc_sampler_init(uint64_t n_nodes, const uint64_t *subtree_sizes,
+                      const uint64_t *parent_ids, const double *branches,
+                      const double *rates, const double *T);
+uint64_t orc_colour_pass(int colour, uint64_t seed, uint64_t sweep, int64_t global0,
+                         uint64_t n_global, uint64_t lo, uint64_t hi);
+void orc_set_row(uint64_t site, uint64_t node, int init_state, uint64_t n, const double *jumps);
+void orc_get_tri_cache(double *out);
+void orc_set_tri_cache(uint64_t site, double v);
 double orc_time_suff_stats(uint64_t reps, double *J, double *D);
 uint64_t orc_end_cond_sample(double r0, double r1, int a, int b, double T,
                              uint64_t cap, double *jumps_out);

@@ -57,6 +57,16 @@ def make_cli():
             param, tree, out + "/sim.paths"])
     open(out + "/mcem_b.log", "w").write("".join(l + "\n" for l in r.stderr.splitlines()
                                                  if l[:1].isdigit() or l.startswith("itr")))
+    # MCEM parameter trajectories of the CPU reference over seeds (for the drop-in CLI test)
+    rows = []
+    for seed in range(1, 13):
+        sh([BIN + "/epievo_est_params_histories", "-s", str(seed), "-i", "3", "-B", "10", "-L", "10",
+            "-o", out + "/_tmp.paths", "-p", out + "/_tmp.param", param, tree, out + "/sim.paths"])
+        vals = [l.split()[1:] for l in open(out + "/_tmp.param")]
+        rows.append("%d\t%s\t%s\t%s\t%s\n" % (seed, vals[0][0], vals[0][1], vals[1][0], vals[1][1]))
+    open(out + "/mcem_seeds.tsv", "w").write("seed\tT00\tT11\tbaseline00\tbaseline11\n" + "".join(rows))
+    os.remove(out + "/_tmp.paths")
+    os.remove(out + "/_tmp.param")
     os.remove(out + "/sim.jumps")
     os.remove(out + "/mcem_b.paths")
 

@@ -1,0 +1,89 @@
+"""The reference's OWN programs, compiled unchanged against the drop-in header
+epievo_b200/host/SingleSiteSampler.hpp and linked with libepievo_b200.so
+(integration/Makefile), run on the GPU: same flags, same files, same outputs."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+from scipy import stats
+
+from epievo_b200.paths import read_paths
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BUILD = os.path.join(ROOT, "integration", "_build")
+CLI = os.path.join(ROOT, "tests", "golden", "cli")
+
+
+def need(binary):
+    p = os.path.join(BUILD, binary)
+    if not os.path.exists(p):
+        pytest.skip("integration/_build not built (make -C integration needs /root/reference)")
+    return p
+
+
+def test_est_params_histories_b200_matches_cpu_reference_over_seeds(tmp_path):
+    """MCEM parameter trajectories: final parameters of `-i 3 -B 10 -L 10` over 12 seeds,
+    GPU-backed binary vs the CPU reference binary (tests/golden/cli/mcem_seeds.tsv).
+    Stated test: two-sample KS and Welch t per parameter, Bonferroni at alpha = 1e-3."""
+    exe = need("epievo_est_params_histories_b200")
+    gold = np.loadtxt(os.path.join(CLI, "mcem_seeds.tsv"), skiprows=1)[:, 1:]
+    got = []
+    for seed in range(101, 113):
+        out, par = str(tmp_path / "o.paths"), str(tmp_path / "o.param")
+        r = subprocess.run([exe, "-s", str(seed), "-i", "3", "-B", "10", "-L", "10", "-o", out, "-p", par,
+                            os.path.join(CLI, "test.param"), os.path.join(CLI, "tree.nwk"),
+                            os.path.join(CLI, "sim.paths")], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        vals = [l.split()[1:] for l in open(par)]
+        got.append([float(vals[0][0]), float(vals[0][1]), float(vals[1][0]), float(vals[1][1])])
+    got = np.array(got)
+    for k, name in enumerate(("T00", "T11", "baseline00", "baseline11")):
+        p_ks = stats.ks_2samp(gold[:, k], got[:, k]).pvalue
+        p_t = stats.ttest_ind(gold[:, k], got[:, k], equal_var=False).pvalue
+        assert min(p_ks, p_t) > 1e-3/8, (name, p_ks, p_t, gold[:, k].mean(), got[:, k].mean())
+    # the output paths file is a valid local-paths file with the leaf data preserved
+    a, b = read_paths(os.path.join(CLI, "sim.paths")), read_paths(out)
+    assert (b.n_sites, b.n_nodes) == (a.n_sites, a.n_nodes) and b.node_names == a.node_names
+    for v in (2, 3, 4):                                   # leaves C, D, F
+        assert np.array_equal(a.end_state()[v], b.end_state()[v])
+
+
+def test_reproducible_with_seed(tmp_path):
+    exe = need("epievo_est_params_histories_b200")
+    outs = []
+    for k in range(2):
+        out, par = str(tmp_path / ("o%d.paths" % k)), str(tmp_path / ("o%d.param" % k))
+        r = subprocess.run([exe, "-s", "7", "-i", "2", "-B", "3", "-L", "2", "-o", out, "-p", par,
+                            os.path.join(CLI, "test.param"), os.path.join(CLI, "tree.nwk"),
+                            os.path.join(CLI, "sim.paths")], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        outs.append((open(out).read(), open(par).read()))
+    assert outs[0] == outs[1]
+
+
+def test_sim_pairwise_b200(tmp_path):
+    """prog/epievo_sim_pairwise.cpp unchanged: its per-site Metropolis_Hastings_site loop
+    becomes one GPU sweep per burn-in iteration."""
+    exe = need("epievo_sim_pairwise_b200")
+    rng = np.random.default_rng(4)
+    n = 500
+    root = (np.cumsum(rng.random(n) > 0.87) & 1)
+    leaf = root ^ (rng.random(n) < 0.3)
+    states = tmp_path / "pair.states"
+    with open(states, "w") as fh:
+        fh.write("#root\tleaf\n")
+        for s in range(n):
+            fh.write("%d\t%d\t%d\n" % (s, root[s], leaf[s]))
+    out = str(tmp_path / "pair.paths")
+    r = subprocess.run([exe, "-s", "3", "-L", "5", "-T", "1.0", "-o", out, os.path.join(CLI, "test.param"),
+                        str(states)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    ps = read_paths(out)
+    assert ps.n_sites == n and ps.n_nodes == 2 and ps.tot_time[1] == 1.0
+    assert np.array_equal(ps.init_state[n:], root.astype(np.uint8))
+    assert np.array_equal(ps.end_state()[1], leaf.astype(np.uint8))
+    j = ps.jumps
+    assert np.all((j > 0) & (j < 1.0))
