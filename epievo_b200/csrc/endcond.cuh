@@ -26,7 +26,8 @@ trunc_exp(double r, double one_minus_e, double U) {
 // if the iteration cap was hit.
 static __device__ __noinline__ int
 end_cond_sample(double rate0, double rate1, int start, int end, double T,
-                double t_off, Philox &rng, double *out, int n, int cap) {
+                double t_off, Philox &rng, double *out, int n, int cap,
+                bool first_jump_given = false) {
   const double s = rate0 + rate1;
   int cur = start;
   double t = 0.0;
@@ -38,7 +39,8 @@ end_cond_sample(double rate0, double rate1, int start, int end, double T,
       if (!(u > 0.0)) return n;
       const double ea = exp(-ra*u), es = exp(-s*u);
       const double p_nojump = ea*s/(rb + ra*es);
-      if (rng.uniform() < p_nojump) return n;
+      // first_jump_given: the caller already drew "at least one jump" for this interval
+      if (!(first_jump_given && iter == 0) && rng.uniform() < p_nojump) return n;
       const double ome_a = -expm1(-ra*u), ome_s = -expm1(-s*u);
       int tries = 0;
       for (;;) {

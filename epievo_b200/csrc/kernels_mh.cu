@@ -12,7 +12,7 @@
 // so each pass reads the old CSR once and writes the new one once; there is no
 // staging buffer and no separate scan/compaction kernel.
 #include "kernels.h"
-#include "mh_site2.cuh"
+#include "mh_flat.cuh"
 
 namespace epv {
 
@@ -47,10 +47,12 @@ tile_base(unsigned long long *desc, uint32_t tile, uint32_t epoch, uint32_t tota
     const int64_t idx = look - lane;
     unsigned long long d;
     bool ready;
-    do {
+    for (unsigned ns = 32;; ns = ns < 1024 ? 2*ns : ns) {
       d = idx >= 0 ? ld_desc(desc + idx) : (tag | FLAG_INC);
       ready = (d >> 34) == epoch && (d & (FLAG_AGG | FLAG_INC)) != 0;
-    } while (__any_sync(0xffffffffu, !ready));
+      if (!__any_sync(0xffffffffu, !ready)) break;
+      __nanosleep(ns);            // back off: a spinning warp must not steal issue slots
+    }
     const unsigned inc = __ballot_sync(0xffffffffu, (d & FLAG_INC) != 0);
     const int first = inc ? __ffs(inc) - 1 : 32;
     uint32_t v = lane <= first ? (uint32_t)d : 0u;
@@ -68,6 +70,7 @@ __global__ void __launch_bounds__(MH_THREADS)
 mh_pass_kernel(const PassArgs a) {
   extern __shared__ uint32_t s_len[];            // [n_branches][MH_THREADS]
   __shared__ ModelParams s_mp;
+  __shared__ CtxTables s_tb;
   __shared__ uint32_t s_tile;
   __shared__ int s_fail;
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
@@ -77,6 +80,7 @@ mh_pass_kernel(const PassArgs a) {
     s_fail = 0;
     s_mp = a.mp;
   }
+  fill_tables(a.mp, s_tb, t);
   __syncthreads();
   const uint32_t tile = s_tile;
   const uint64_t g = (uint64_t)tile*MH_THREADS + t;     // group of sites 3g..3g+2
@@ -85,27 +89,45 @@ mh_pass_kernel(const PassArgs a) {
   const int64_t gsite = a.global0 + (int64_t)st;
 
   // ---- phase 1: the update -------------------------------------------------------
-  double q[2*MAXN];
+  constexpr int PB = 16, QCAP = 8;
+  FlatScratch<MAXN, PB, QCAP> S;
   double pj_local[MAXJ];
   uint16_t pn[MAXN];
   uint8_t pend[MAXN];
   Proposal pr; pr.pj = pj_local; pr.cap = MAXJ; pr.pn = pn; pr.pend = pend;
   int accepted = 0, total = 0;
-  if (st >= a.upd_lo && st < a.upd_hi && gsite >= 1 && gsite + 1 < (int64_t)a.n_global) {
+  {
+    const bool active = st >= a.upd_lo && st < a.upd_hi && gsite >= 1 && gsite + 1 < (int64_t)a.n_global;
     SiteCtx c; c.pv = a.in; c.state = a.state; c.W = a.W; c.tree = a.tree; c.site = st;
-    int r = mh_site(s_mp, c, a.state, a.tri_llh, a.seed, a.sweep, (uint64_t)gsite,
-                    a.n_global, q, pr, total);
-    if (r == -1) {        // proposal longer than the per-thread buffer: global scratch
-      const uint32_t slot = atomicAdd(a.scratch_ctr, 1u);
-      if (slot >= a.scratch_slots) { atomicOr(a.err, ERR_SCRATCH_SLOTS); r = 0; }
-      else {
-        pr.pj = a.scratch + (uint64_t)slot*a.scratch_cap; pr.cap = (int)a.scratch_cap;
-        r = mh_site(s_mp, c, a.state, a.tri_llh, a.seed, a.sweep, (uint64_t)gsite,
-                    a.n_global, q, pr, total);
-        if (r == -1) { atomicOr(a.err, ERR_SCRATCH_SIZE); r = 0; }
+    int r = mh_site_flat<MAXN, PB, QCAP>(active, s_mp, s_tb, c, a.state, a.tri_llh, a.seed, a.sweep,
+                                         (uint64_t)gsite, a.n_global, S, pr, total);
+    // -3: interval stack too small -- a property of the neighbours' rows only, so switching
+    // to the generic per-branch routine here is unbiased (rare; runs divergently)
+    const bool generic = r == -3;
+    if (generic)
+      r = mh_site(s_mp, c, a.state, a.tri_llh, a.seed, a.sweep, (uint64_t)gsite, a.n_global,
+                  S.q, pr, total);
+    // -1: proposal longer than the per-thread buffer: rerun with a global scratch slot and
+    // the same streams (=> the same proposal).  The flat routine is warp-synchronous, so the
+    // whole warp re-enters it with only the overflowing lanes active.
+    if (__any_sync(0xffffffffu, r == -1)) {
+      const bool again = r == -1;
+      if (again) {
+        const uint32_t slot = atomicAdd(a.scratch_ctr, 1u);
+        if (slot >= a.scratch_slots) { atomicOr(a.err, ERR_SCRATCH_SLOTS); r = 0; }
+        else { pr.pj = a.scratch + (uint64_t)slot*a.scratch_cap; pr.cap = (int)a.scratch_cap; }
       }
+      const bool redo = again && r == -1;
+      const int r2 = mh_site_flat<MAXN, PB, QCAP>(redo && !generic, s_mp, s_tb, c, a.state, a.tri_llh,
+                                                  a.seed, a.sweep, (uint64_t)gsite, a.n_global, S, pr, total);
+      if (redo && !generic) r = r2;
+      if (redo && generic)
+        r = mh_site(s_mp, c, a.state, a.tri_llh, a.seed, a.sweep, (uint64_t)gsite, a.n_global,
+                    S.q, pr, total);
+      if (r == -1) { atomicOr(a.err, ERR_SCRATCH_SIZE); r = 0; }
     }
     if (r == -2) { atomicOr(a.err, ERR_SAMPLER_STUCK); r = 0; }
+    if (r < 0) r = 0;
     accepted = r;
   }
   const unsigned acc_mask = __ballot_sync(0xffffffffu, accepted);

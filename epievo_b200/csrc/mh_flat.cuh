@@ -1,0 +1,279 @@
+// mh_flat.cuh -- the Metropolis-Hastings site update restructured for SIMT.
+//
+// Same mathematics as mh_site (mh_site2.cuh; SingleSiteSampler.cpp:482-536), different
+// control flow.  The nested "for branch { for interval { ... } }" loops, whose trip
+// counts differ between the 32 sites of a warp, are flattened into single loops whose
+// iteration is one unit of work (one neighbour interval, one jump event), so a warp
+// runs max-over-lanes of the per-site TOTAL instead of the sum over branches of the
+// per-branch maximum:
+//   1. upward pruning: one interval per iteration, backward in time, branches in reverse
+//      preorder; partial vectors p[i] (and exp terms h_i) of multi-interval branches go
+//      to a small per-thread stack that the downward pass pops in exactly reverse order;
+//   2. downward pass: one interval per iteration; draws the interval's end state and,
+//      when start == end, the "no jump at all" Bernoulli; intervals that need jump times
+//      are queued (FIFO), not sampled inline;
+//   3. the queue is drained with end_cond_sample (rare work, done with the lanes that
+//      have it);
+//   4. the three triple log-likelihoods of the proposal come from ONE five-way merge per
+//      branch over the rows of sites s-2..s+2, one event per iteration.
+// Transition probabilities use per-context tables (pi0 = r0/s, pi1 = r1/s, s): no fp64
+// division; the end-state and no-jump draws compare products instead of ratios.
+#pragma once
+#include "mh_site2.cuh"
+
+namespace epv {
+
+struct CtxTables {          // indexed by ctx = l*4 + r (mid bit clear): 0, 1, 4, 5
+  double s[8], pi0[8], pi1[8];
+};
+
+__device__ __forceinline__ void
+fill_tables(const ModelParams &mp, CtxTables &tb, int t) {
+  if (t < 8) {
+    const int ctx = t & ~2;
+    const double r0 = mp.rate[ctx], r1 = mp.rate[ctx | 2], s = r0 + r1;
+    tb.s[t] = s; tb.pi0[t] = r0/s; tb.pi1[t] = r1/s;
+  }
+}
+
+// Rows of sites s-1, s, s+1 on branch bi (own row: count only).
+__device__ __forceinline__ void
+load_lmr(const PathView &pv, const uint8_t *state, int W, int bi, uint64_t site,
+         Row &L, Row &R, int &own_n) {
+  if (site - 1 >= pv.own_lo && site + 1 < pv.own_hi) {
+    const uint32_t *o = pv.off + (uint64_t)bi*pv.off_pitch + (site - 1 - pv.own_lo);
+    const uint32_t o0 = o[0], o1 = o[1], o2 = o[2], o3 = o[3];
+    const double *base = pv.jmp + pv.jbase[bi];
+    L.ptr = base + o0; L.n = (int)(o1 - o0);
+    own_n = (int)(o2 - o1);
+    R.ptr = base + o2; R.n = (int)(o3 - o2);
+    L.init = state_bit(state, W, site - 1, bi + 1);
+    R.init = state_bit(state, W, site + 1, bi + 1);
+  }
+  else {
+    L = load_row(pv, state, W, bi, site - 1);
+    R = load_row(pv, state, W, bi, site + 1);
+    own_n = load_row(pv, state, W, bi, site).n;
+  }
+}
+
+struct QItem { double t_off, len; int v; int code; };   // code: ctx | cur<<3 | end<<4
+
+template <int MAXN, int PB, int QCAP>
+struct FlatScratch {
+  double q[2*MAXN];
+  double hb[MAXN];
+  double stk[3*PB];
+  QItem queue[QCAP];
+};
+
+// Drain the queue of intervals that need jump times (FIFO keeps pj in branch/time order).
+template <int QCAP>
+__device__ __forceinline__ int
+drain_queue(const ModelParams &mp, QItem *queue, int &qn, Philox &rng, Proposal &pr, int total) {
+  for (int k = 0; k < qn; ++k) {
+    const QItem it = queue[k];
+    const int ctx = it.code & 7, cur = (it.code >> 3) & 1, end = (it.code >> 4) & 1;
+    const int before = total;
+    total = end_cond_sample(mp.rate[ctx], mp.rate[ctx | 2], cur, end, it.len, it.t_off, rng,
+                            pr.pj, total, pr.cap, cur == end);
+    if (total < 0) return total;
+    const int add = total - before + pr.pn[it.v];
+    if (add > 65535) return -1;
+    pr.pn[it.v] = (uint16_t)add;
+  }
+  qn = 0;
+  return total;
+}
+
+// Returns 1 accepted, 0 rejected (or inactive lane), -1 proposal buffer too small (rerun
+// with a larger one: same streams, same proposal), -2 sampler stuck, -3 interval stack too
+// small (depends on the neighbours' rows only; the caller falls back to mh_site).
+//
+// WARP-SYNCHRONOUS: must be called by all 32 lanes of a warp together (lanes without a
+// site to update pass active = false).  Every flat loop runs `while (__any_sync(...))`,
+// so its trip count is warp-uniform and the lanes reconverge every iteration; there are
+// no early returns (a failing lane records its status and idles).  Without this the
+// compiler leaves lanes that left a loop at different iterations diverged for the rest
+// of the function (measured: 2-4 active lanes per instruction).
+template <int MAXN, int PB, int QCAP>
+__device__ __forceinline__ int
+mh_site_flat(bool active, const ModelParams &mp, const CtxTables &tb, const SiteCtx &c,
+             uint8_t *state_rw, double *tri_llh, uint64_t seed, uint32_t sweep, uint64_t gsite,
+             uint64_t n_global, FlatScratch<MAXN, PB, QCAP> &S, Proposal &pr, int &total_out) {
+  constexpr unsigned FULL = 0xffffffffu;
+  const int n_nodes = c.tree.n_nodes;
+  const uint64_t s = c.site;
+  double *q = S.q;
+  int status = 1;                       // becomes <0 on failure; the lane then idles
+
+  // ---- 1. upward pruning, flat over (branch, interval) ----------------------------
+  for (int v = 0; v < n_nodes; ++v) { q[2*v] = 1.0; q[2*v + 1] = 1.0; pr.pn[v] = 0; }
+  int sp = 0;
+  {
+    int v = active ? n_nodes - 1 : 0;
+    RevMerge m;
+    double p0 = 0.0, p1 = 0.0;
+    bool need_init = true;
+    while (__any_sync(FULL, v >= 1)) {
+      if (v < 1) continue;
+      if (need_init) {
+        Row L, R; int own_n;
+        load_lmr(c.pv, c.state, c.W, v - 1, s, L, R, own_n);
+        m.start(L, R, c.tree.branch[v]);
+        if (c.tree.subtree[v] == 1) {
+          const int leaf = state_bit(c.state, c.W, s, v) ^ (own_n & 1);
+          p0 = leaf ? 0.0 : 1.0; p1 = leaf ? 1.0 : 0.0;
+          q[2*v] = p0; q[2*v + 1] = p1;
+        }
+        else { p0 = q[2*v]; p1 = q[2*v + 1]; }
+        need_init = false;
+      }
+      double len; int ctx; bool first;
+      m.next(len, ctx, first);
+      const double h = exp(-len*tb.s[ctx]);
+      const double P00 = tb.pi1[ctx] + tb.pi0[ctx]*h, P11 = tb.pi0[ctx] + tb.pi1[ctx]*h;
+      const double a = P00*p0 + (1.0 - P00)*p1, b = (1.0 - P11)*p0 + P11*p1;
+      p0 = a; p1 = b;
+      if (first) {
+        S.hb[v] = h;
+        const int par = c.tree.parent[v];
+        q[2*par] *= p0; q[2*par + 1] *= p1;
+        --v; need_init = true;
+      }
+      else if (sp >= PB) { status = -3; v = 0; }
+      else { S.stk[3*sp] = p0; S.stk[3*sp + 1] = p1; S.stk[3*sp + 2] = h; ++sp; }
+    }
+  }
+
+  // ---- 2. downward pass, flat over (branch, interval) -----------------------------
+  Philox rng; rng.init(seed, sweep, gsite, 1u);
+  pr.pend[0] = active ? (uint8_t)state_bit(c.state, c.W, s, 1) : 0;
+  int total = 0, qn = 0;
+  {
+    int v = (active && status > 0) ? 1 : n_nodes, prev = 0, i = 0;
+    FwdMerge m;
+    double passed = 0.0, h_saved = 0.0;
+    bool need_init = true;
+    while (__any_sync(FULL, v < n_nodes)) {
+      if (v >= n_nodes) continue;
+      if (need_init) {
+        Row L, R; int own_n;
+        load_lmr(c.pv, c.state, c.W, v - 1, s, L, R, own_n);
+        m.start(L, R, c.tree.branch[v]);
+        prev = pr.pend[c.tree.parent[v]];
+        passed = 0.0; i = 0; need_init = false;
+      }
+      double len; int ctx; bool last;
+      m.next(len, ctx, last);
+      const double h = i == 0 ? S.hb[v] : h_saved;
+      double nx0, nx1;
+      if (last) { nx0 = q[2*v]; nx1 = q[2*v + 1]; }
+      else { --sp; nx0 = S.stk[3*sp]; nx1 = S.stk[3*sp + 1]; h_saved = S.stk[3*sp + 2]; }
+      const double P00 = tb.pi1[ctx] + tb.pi0[ctx]*h, P11 = tb.pi0[ctx] + tb.pi1[ctx]*h;
+      const double to0 = prev ? 1.0 - P11 : P00, to1 = prev ? P11 : 1.0 - P00;
+      const double a0 = to0*nx0, a1 = to1*nx1;
+      const int e = rng.uniform()*(a0 + a1) > a0;          // end state of the interval
+      bool need_jumps = e != prev;
+      if (!need_jumps) {
+        // P(no jump | start == end) = exp(-r_prev len) / P(prev -> prev)
+        const double ea = exp(-len*(prev ? mp.rate[ctx | 2] : mp.rate[ctx]));
+        need_jumps = !(rng.uniform()*(prev ? P11 : P00) < ea);
+      }
+      if (need_jumps) {
+        if (qn == QCAP) total = drain_queue<QCAP>(mp, S.queue, qn, rng, pr, total);
+        if (total < 0) { status = total; v = n_nodes; continue; }
+        QItem it; it.t_off = passed; it.len = len; it.v = v; it.code = ctx | (prev << 3) | (e << 4);
+        S.queue[qn++] = it;
+      }
+      passed += len; prev = e; ++i;
+      if (last) { pr.pend[v] = (uint8_t)prev; ++v; need_init = true; }
+    }
+  }
+  // ---- 3. jump times of the queued intervals ---------------------------------------
+  if (status > 0) {
+    total = drain_queue<QCAP>(mp, S.queue, qn, rng, pr, total);
+    if (total < 0) status = total;
+  }
+  __syncwarp(FULL);
+  total_out = total;
+
+  // ---- 4. the three triple log-likelihoods: one five-way merge per branch ----------
+  const bool live = active && status > 0;
+  const bool do_l = live && gsite > 1, do_r = live && gsite + 2 < n_global;
+  const double l_old = live ? tri_llh[s - 1] : 0.0, r_old = live ? tri_llh[s + 1] : 0.0;
+  double xl = 0.0, xm = 0.0, xr = 0.0;
+  if (live) {
+    const int sm = pr.pend[0];
+    const int sl1 = state_bit(c.state, c.W, s - 1, 1), sr1 = state_bit(c.state, c.W, s + 1, 1);
+    xm = mp.T[sl1*2 + sm]*mp.T[sm*2 + sr1];
+    xl = do_l ? mp.T[state_bit(c.state, c.W, s - 2, 1)*2 + sl1]*mp.T[sl1*2 + sm] : l_old;
+    xr = do_r ? mp.T[sm*2 + sr1]*mp.T[sr1*2 + state_bit(c.state, c.W, s + 2, 1)] : r_old;
+  }
+  {
+    const double INF = __longlong_as_double(0x7ff0000000000000LL);
+    int v = live ? 1 : n_nodes, poff = 0;
+    Row A, B, P, C, E;
+    A.n = B.n = P.n = C.n = E.n = 0; A.ptr = B.ptr = P.ptr = C.ptr = E.ptr = pr.pj;
+    int iA = 0, iB = 0, iP = 0, iC = 0, iE = 0, bits = 0;   // bits: A<<4 | B<<3 | P<<2 | C<<1 | E
+    double prev_l = 0.0, prev_m = 0.0, prev_r = 0.0, tot = 0.0;
+    bool need_init = true;
+    while (__any_sync(FULL, v < n_nodes)) {
+      if (v >= n_nodes) continue;
+      if (need_init) {
+        const int bi = v - 1;
+        B = load_row(c.pv, c.state, c.W, bi, s - 1);
+        C = load_row(c.pv, c.state, c.W, bi, s + 1);
+        if (do_l) A = load_row(c.pv, c.state, c.W, bi, s - 2); else { A.n = 0; A.init = 0; A.ptr = B.ptr; }
+        if (do_r) E = load_row(c.pv, c.state, c.W, bi, s + 2); else { E.n = 0; E.init = 0; E.ptr = C.ptr; }
+        P.ptr = pr.pj + poff; P.n = pr.pn[v]; P.init = pr.pend[c.tree.parent[v]];
+        poff += P.n;
+        iA = iB = iP = iC = iE = 0;
+        bits = A.init << 4 | B.init << 3 | P.init << 2 | C.init << 1 | E.init;
+        prev_l = prev_m = prev_r = 0.0;
+        tot = c.tree.branch[v];
+        need_init = false;
+      }
+      // next event: smallest time, ties to the higher site index (the reference's
+      // right-before-mid-before-left rule, Path.cpp:275-281, holds for all three triples)
+      double t = iE < E.n ? E.ptr[iE] : INF; int k = 0;
+      { const double x = iC < C.n ? C.ptr[iC] : INF; if (x < t) { t = x; k = 1; } }
+      { const double x = iP < P.n ? P.ptr[iP] : INF; if (x < t) { t = x; k = 2; } }
+      { const double x = iB < B.n ? B.ptr[iB] : INF; if (x < t) { t = x; k = 3; } }
+      { const double x = iA < A.n ? A.ptr[iA] : INF; if (x < t) { t = x; k = 4; } }
+      const bool done = !(t < INF);
+      if (done) t = tot;
+      const int tl = bits >> 2, tm = (bits >> 1) & 7, tr = bits & 7;
+      if (do_l && (k >= 2 || done)) { xl -= mp.rate[tl]*(t - prev_l); prev_l = t; }
+      if ((k >= 1 && k <= 3) || done) { xm -= mp.rate[tm]*(t - prev_m); prev_m = t; }
+      if (do_r && (k <= 2 || done)) { xr -= mp.rate[tr]*(t - prev_r); prev_r = t; }
+      if (done) { ++v; need_init = true; }
+      else {
+        if (k == 3 && do_l) xl += mp.log_rate[tl];      // mid of the left triple jumped
+        if (k == 2) xm += mp.log_rate[tm];
+        if (k == 1 && do_r) xr += mp.log_rate[tr];
+        bits ^= 1 << k;
+        iE += k == 0; iC += k == 1; iP += k == 2; iB += k == 3; iA += k == 4;
+      }
+    }
+  }
+
+  // ---- accept / reject (log_accept_rate, SingleSiteSampler.cpp:396-433, :520-533) ---
+  if (!live) return active ? status : 0;
+  const double llr = (xl + xr) - l_old - r_old;
+  Philox rng0; rng0.init(seed, sweep, gsite, 0u);
+  const double u = rng0.uniform();
+  if (!(llr >= 0.0 || u < exp(llr))) return 0;
+  tri_llh[s - 1] = xl; tri_llh[s] = xm; tri_llh[s + 1] = xr;
+  for (int w = 0; w < c.W; ++w) {
+    unsigned sb = 0;
+    for (int k = 0; k < 8; ++k) {
+      const int v = w*8 + k;
+      if (v >= 1 && v < n_nodes) sb |= (unsigned)pr.pend[c.tree.parent[v]] << k;
+    }
+    state_rw[s*c.W + w] = (uint8_t)sb;
+  }
+  return 1;
+}
+
+}  // namespace epv

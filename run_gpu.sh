@@ -1,4 +1,10 @@
 mkdir -p gpurun_out
-nvidia-smi -L
-python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 2 --warmup 3 > gpurun_out/bench_n2.log 2> gpurun_out/bench_n2.err; echo "bench2 rc=$?"; tail -c 2500 gpurun_out/bench_n2.log; tail -15 gpurun_out/bench_n2.err
-python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29512 tools/dist_check.py > gpurun_out/dist_check.log 2>&1; echo "distcheck rc=$?"; tail -8 gpurun_out/dist_check.log
+python -m pytest tests -m gpu -q -x > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -30 gpurun_out/pytest_gpu.log
+python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/bench.log 2> gpurun_out/bench.err; echo "bench rc=$?"; python - <<'PY'
+import json
+d=json.loads(open('gpurun_out/bench.log').read().strip().splitlines()[-1])
+print(d['value'], d['e2e']['value'], d['roofline']['avg_launch_ms'], d['acc_rate'])
+PY
+tail -3 gpurun_out/bench.err
+B="python bench.py --steps 1 --warmup 1 --sites 2000000 --burn-in 2 --batch 2 --no-e2e --no-cpu-baseline"
+$B > gpurun_out/plain2.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:mh_pass -s 12 -c 2 -o gpurun_out/prof_mh $B > gpurun_out/ncu2.log 2>&1
