@@ -22,7 +22,8 @@ void free_paths(epv_ctx *c) {
   }
   cudaFree(c->d_jbase); cudaFree(c->d_jcap); cudaFree(c->d_state); cudaFree(c->d_tri);
   cudaFree(c->d_desc); cudaFree(c->d_hcnt); cudaFree(c->d_hjmp);
-  cudaFree(c->d_stage_init); cudaFree(c->d_stage_off);
+  cudaFree(c->d_stage_init); cudaFree(c->d_stage_off); cudaFree(c->d_stg_off); cudaFree(c->d_stg);
+  c->d_stg_off = nullptr; c->d_stg = nullptr;
   c->d_hcnt = nullptr; c->d_hjmp = nullptr; c->d_stage_init = nullptr; c->d_stage_off = nullptr;
   c->d_jbase = c->d_jcap = nullptr; c->d_state = nullptr; c->d_tri = nullptr;
   c->d_desc = nullptr;
@@ -41,6 +42,7 @@ int check_device_flags(epv_ctx *c) {
   if (flags & ERR_SCRATCH_SIZE) m += " a proposed path exceeds the per-site scratch capacity;";
   if (flags & ERR_SAMPLER_STUCK) m += " end-conditioned sampler did not terminate;";
   if (flags & ERR_BAD_INPUT) m += " malformed input;";
+  if (flags & ERR_STAGE_CAPACITY) m += " proposal staging buffer exceeded;";
   if (flags & ERR_HALO_CAPACITY) m += " a shard-boundary row has more jumps than a halo record holds;";
   if (flags & ERR_HALO_MISMATCH) m += " a halo record arrived for the wrong site (driver / colour mismatch);";
   return fail(c, m + " paths on the device are no longer valid");
@@ -69,6 +71,7 @@ int epv_create(epv_ctx **out, int device) {
     && cudaMalloc(&c->d_nacc, sizeof(unsigned long long)) == cudaSuccess
     && cudaMalloc(&c->d_ticket, sizeof(uint32_t)) == cudaSuccess
     && cudaMalloc(&c->d_scratch_ctr, sizeof(uint32_t)) == cudaSuccess
+    && cudaMalloc(&c->d_stg_ctr, sizeof(unsigned long long)) == cudaSuccess
     && cudaMalloc(&c->d_out9, 9*sizeof(double)) == cudaSuccess
     && cudaMalloc(&c->d_mail, 4096*sizeof(unsigned long long)) == cudaSuccess
     && cudaMallocHost(&c->h_mail, 4096*sizeof(unsigned long long)) == cudaSuccess
@@ -99,6 +102,7 @@ void epv_destroy(epv_ctx *c) {
   free_paths(c);
   cudaFree(c->d_parent); cudaFree(c->d_subtree); cudaFree(c->d_branch);
   cudaFree(c->d_err); cudaFree(c->d_nacc); cudaFree(c->d_ticket); cudaFree(c->d_scratch_ctr);
+  cudaFree(c->d_stg_ctr);
   cudaFree(c->d_scratch); cudaFree(c->d_out9); cudaFree(c->d_mail); cudaFreeHost(c->h_mail);
   cudaFree(c->d_J); cudaFree(c->d_D); cudaFree(c->d_Jsum); cudaFree(c->d_Dsum); cudaFree(c->d_ss);
   cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1);

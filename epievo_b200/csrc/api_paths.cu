@@ -41,6 +41,21 @@ static int alloc_jumps(epv_ctx *c, const std::vector<uint64_t> &cap, double *out
   return 0;
 }
 
+// Staging blob for the accepted proposals of ONE colour pass: at most one header per
+// group (ceil(n_br/4) words of u16 counts) plus the new jump times of a third of the rows
+// (sized at half of the total jump capacity).
+int alloc_stage(epv_ctx *c) {
+  const uint64_t n_br = c->n_nodes - 1;
+  c->n_groups = (c->n_sites + 2)/3;
+  const unsigned long long cap = c->n_groups*((n_br + 3)/4) + c->jmp_total_cap/2 + 4096;
+  if (c->d_stg && cap <= c->stg_cap) return 0;
+  cudaFree(c->d_stg); c->d_stg = nullptr;
+  EPV_CUDA(c, cudaMalloc(&c->d_stg, cap*sizeof(double)));
+  c->stg_cap = cap;
+  if (!c->d_stg_off) EPV_CUDA(c, cudaMalloc(&c->d_stg_off, c->n_groups*sizeof(uint32_t)));
+  return 0;
+}
+
 // Grow any branch whose fill exceeds 3/4 of its capacity (called between sweeps).
 int maybe_regrow(epv_ctx *c, const std::vector<uint64_t> &tot) {
   const int n_br = c->n_nodes - 1;
@@ -62,7 +77,7 @@ int maybe_regrow(epv_ctx *c, const std::vector<uint64_t> &tot) {
   cudaFree(c->d_jmp[0]); cudaFree(c->d_jmp[1]);
   c->d_jmp[0] = nj[0]; c->d_jmp[1] = nj[1];
   c->h_jbase = base; c->h_jcap = cap; c->jmp_total_cap = total;
-  return 0;
+  return alloc_stage(c);
 }
 
 }  // namespace epv
@@ -143,6 +158,7 @@ int epv_upload_paths(epv_ctx *c, uint64_t n_sites, uint64_t n_nodes, const uint8
     const uint64_t n_rows = n_nodes*n_sites;
     EPV_CUDA(c, cudaMalloc(&c->d_stage_init, n_rows));
     EPV_CUDA(c, cudaMalloc(&c->d_stage_off, (n_rows + 1)*sizeof(unsigned long long)));
+    if (int r = alloc_stage(c)) return r;
     EPV_CUDA(c, cudaMemsetAsync(c->d_desc, 0, (size_t)n_br*c->n_tiles*sizeof(unsigned long long), c->stream));
     c->epoch = 0;
     EPV_CUDA(c, cudaMemcpyAsync(c->d_jbase, c->h_jbase.data(), n_br*sizeof(uint64_t), cudaMemcpyHostToDevice, c->stream));

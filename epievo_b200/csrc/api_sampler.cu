@@ -66,7 +66,10 @@ int one_pass(epv_ctx *c, int colour, uint64_t seed, uint32_t sweep) {
   a.scratch = c->d_scratch; a.scratch_ctr = c->d_scratch_ctr;
   a.scratch_slots = c->scratch_slots; a.scratch_cap = c->scratch_cap;
   a.err = c->d_err; a.n_accept = c->d_nacc;
+  a.n_groups = c->n_groups; a.stage_off = c->d_stg_off; a.stage = c->d_stg;
+  a.stage_ctr = c->d_stg_ctr; a.stage_cap = c->stg_cap;
   EPV_CUDA(c, cudaMemsetAsync(c->d_scratch_ctr, 0, sizeof(uint32_t), c->stream));
+  EPV_CUDA(c, cudaMemsetAsync(c->d_stg_ctr, 0, sizeof(unsigned long long), c->stream));
   if (c->timing) {
     if (c->ev_pending == epv_ctx::EV_RING) drain_timing(c);
     cudaEventRecord(c->ev_ring[2*c->ev_pending], c->stream);
@@ -76,7 +79,8 @@ int one_pass(epv_ctx *c, int colour, uint64_t seed, uint32_t sweep) {
     cudaEventRecord(c->ev_ring[2*c->ev_pending + 1], c->stream);
     ++c->ev_pending;
   }
-  ++c->launches; ++c->mh_launches;
+  launch_csr_rebuild(a, c->stream);
+  c->launches += 2; ++c->mh_launches;
   c->ticket_base += c->n_tiles;
   c->cur ^= 1;
   c->stats_valid = false;

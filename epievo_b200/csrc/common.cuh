@@ -17,6 +17,7 @@ enum : unsigned {
   ERR_BAD_INPUT     = 16u,
   ERR_HALO_CAPACITY = 32u,  // a boundary row has more than HALO_K jumps
   ERR_HALO_MISMATCH = 64u,  // a halo record arrived for another site / colour
+  ERR_STAGE_CAPACITY = 128u,// accepted proposals of one pass exceed the staging buffer
 };
 
 // ---- model constants, one copy in __constant__ memory per context upload ---------
@@ -95,6 +96,16 @@ struct Philox {
   to_unit(uint32_t hi, uint32_t lo) {
     const uint64_t k = (((uint64_t)hi << 32) | lo) >> 12;
     return ((double)k + 0.5)*2.220446049250313e-16;
+  }
+
+  // two uniforms from one fresh block (keeps the lanes of a warp converged: no
+  // data-dependent "spare" state)
+  __device__ __forceinline__ void
+  uniform2(double &u1, double &u2) {
+    uint32_t r0, r1, r2, r3;
+    block(r0, r1, r2, r3);
+    ++c3;
+    u1 = to_unit(r0, r1); u2 = to_unit(r2, r3);
   }
 
   __device__ __forceinline__ double

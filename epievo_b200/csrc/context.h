@@ -38,6 +38,11 @@ struct epv_ctx {
   double *d_tri = nullptr;
   bool tri_valid = false;
 
+  // staging of accepted proposals between the update and the rebuild kernel
+  uint32_t *d_stg_off = nullptr;             // [n_groups]
+  double *d_stg = nullptr;
+  unsigned long long stg_cap = 0, *d_stg_ctr = nullptr;
+  uint64_t n_groups = 0;
   // colour-pass machinery
   unsigned long long *d_desc = nullptr;
   uint32_t n_tiles = 0, epoch = 0, ticket_base = 0;

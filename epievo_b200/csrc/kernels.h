@@ -34,11 +34,18 @@ struct PassArgs {
   double *scratch;
   uint32_t *scratch_ctr;
   uint32_t scratch_slots, scratch_cap;
+  // staging of the accepted proposals' rows between the update and the rebuild kernel
+  uint64_t n_groups;          // groups of 3 sites covering the local sites
+  uint32_t *stage_off;        // [n_groups] offset into stage, or rejected / empty marker
+  double *stage;              // blobs: ceil(n_br/4) words of u16 jump counts + jump times
+  unsigned long long *stage_ctr;
+  unsigned long long stage_cap;
   unsigned *err;
   unsigned long long *n_accept;
 };
 
-void launch_mh_pass(const PassArgs &a, cudaStream_t st);
+void launch_mh_pass(const PassArgs &a, cudaStream_t st);       // update kernel
+void launch_csr_rebuild(const PassArgs &a, cudaStream_t st);   // re-compaction kernel
 size_t mh_pass_smem_bytes(int n_nodes);
 
 void launch_tri_llh(const ModelParams &mp, const PathView &pv, const uint8_t *state, int W,

@@ -1,16 +1,22 @@
-// kernels_mh.cu -- the Metropolis-Hastings colour-pass kernel.
+// kernels_mh.cu -- one stride-3 colour pass of the Metropolis-Hastings sweep
+// (SingleSiteSampler::single_iteration, SingleSiteSampler.cpp:538-548, re-ordered into
+// stride-3 colour classes: updates of s and s+3 touch disjoint data), as TWO kernels:
 //
-// One launch updates every site s == colour (mod 3) of the shard
-// (SingleSiteSampler::single_iteration, SingleSiteSampler.cpp:538-548, re-ordered
-// into stride-3 colour classes: updates of s and s+3 touch disjoint data) AND rebuilds
-// the per-branch CSR in the ping-pong buffer in the same pass:
-//   phase 1  one thread per group of 3 sites runs mh_site() for the group's target
-//   phase 2  per branch, the new row lengths of the tile are summed per thread
-//   phase 3  per branch, one warp scans the tile and obtains the tile's base offset
-//            with a single-pass chained scan (decoupled look-back) across tiles
-//   phase 4  every thread writes its 3 rows' offsets and jump times to the new CSR
-// so each pass reads the old CSR once and writes the new one once; there is no
-// staging buffer and no separate scan/compaction kernel.
+//   mh_update_kernel    one thread per group of 3 sites runs the update of the group's
+//                       site of the pass's colour (mh_site_flat).  State bits and tri_llh
+//                       are updated in place; an accepted proposal's rows go to a
+//                       staging blob (u16 jump counts per branch + jump times), found
+//                       through stage_off[group].
+//   csr_rebuild_kernel  re-compacts the per-branch CSR into the ping-pong partner:
+//                       per branch, new row lengths -> tile scan -> single-pass chained
+//                       scan (decoupled look-back) across tiles -> offsets and jump
+//                       times written in site order.  Pure streaming, every tile costs
+//                       the same, so the look-back never waits for long.
+//
+// The two were one kernel at first.  ncu showed a third of its instructions in the
+// look-back spin: tiles whose updates finished early waited, holding their SM slots, for
+// the slowest earlier tile (update time varies with the rows' jump counts).  Splitting
+// costs one staging round trip of the accepted proposals (a few % of the row bytes).
 #include "kernels.h"
 #include "mh_flat.cuh"
 
@@ -18,6 +24,91 @@ namespace epv {
 
 namespace {
 
+constexpr uint32_t STG_REJECTED = 0xffffffffu, STG_EMPTY = 0xfffffffeu;
+
+__device__ __forceinline__ int stage_header_words(int n_br) { return (n_br + 3) >> 2; }
+
+template <int MAXN, int MAXJ>
+__global__ void __launch_bounds__(MH_THREADS)
+mh_update_kernel(const PassArgs a) {
+  __shared__ ModelParams s_mp;
+  __shared__ CtxTables s_tb;
+  const int t = threadIdx.x, lane = t & 31;
+  const int n_br = a.tree.n_nodes - 1;
+  if (t == 0) s_mp = a.mp;
+  fill_tables(a.mp, s_tb, t);
+  __syncthreads();
+  const uint64_t g = (uint64_t)blockIdx.x*MH_THREADS + t;     // group of sites 3g..3g+2
+  const uint64_t st = 3*g + a.colour;                          // the group's target site
+  const int64_t gsite = a.global0 + (int64_t)st;
+
+  constexpr int PB = 16, QCAP = 8;
+  FlatScratch<MAXN, PB, QCAP> S;
+  double pj_local[MAXJ];
+  uint16_t pn[MAXN];
+  uint8_t pend[MAXN];
+  Proposal pr; pr.pj = pj_local; pr.cap = MAXJ; pr.pn = pn; pr.pend = pend;
+  int accepted = 0, total = 0;
+  {
+    const bool active = st >= a.upd_lo && st < a.upd_hi && gsite >= 1 && gsite + 1 < (int64_t)a.n_global;
+    SiteCtx c; c.pv = a.in; c.state = a.state; c.W = a.W; c.tree = a.tree; c.site = st;
+    int r = mh_site_flat<MAXN, PB, QCAP>(active, s_mp, s_tb, c, a.state, a.tri_llh, a.seed, a.sweep,
+                                         (uint64_t)gsite, a.n_global, S, pr, total);
+    // -3: interval stack too small -- a property of the neighbours' rows only, so switching
+    // to the generic per-branch routine here is unbiased (rare; runs divergently)
+    const bool generic = r == -3;
+    if (generic)
+      r = mh_site(s_mp, c, a.state, a.tri_llh, a.seed, a.sweep, (uint64_t)gsite, a.n_global,
+                  S.q, pr, total);
+    // -1: proposal longer than the per-thread buffer: rerun with a global scratch slot and
+    // the same streams (=> the same proposal).  The flat routine is warp-synchronous, so the
+    // whole warp re-enters it with only the overflowing lanes active.
+    if (__any_sync(0xffffffffu, r == -1)) {
+      const bool again = r == -1;
+      if (again) {
+        const uint32_t slot = atomicAdd(a.scratch_ctr, 1u);
+        if (slot >= a.scratch_slots) { atomicOr(a.err, ERR_SCRATCH_SLOTS); r = 0; }
+        else { pr.pj = a.scratch + (uint64_t)slot*a.scratch_cap; pr.cap = (int)a.scratch_cap; }
+      }
+      const bool redo = again && r == -1;
+      const int r2 = mh_site_flat<MAXN, PB, QCAP>(redo && !generic, s_mp, s_tb, c, a.state, a.tri_llh,
+                                                  a.seed, a.sweep, (uint64_t)gsite, a.n_global, S, pr, total);
+      if (redo && !generic) r = r2;
+      if (redo && generic)
+        r = mh_site(s_mp, c, a.state, a.tri_llh, a.seed, a.sweep, (uint64_t)gsite, a.n_global,
+                    S.q, pr, total);
+      if (r == -1) { atomicOr(a.err, ERR_SCRATCH_SIZE); r = 0; }
+    }
+    if (r == -2) { atomicOr(a.err, ERR_SAMPLER_STUCK); r = 0; }
+    if (r < 0) r = 0;
+    accepted = r;
+  }
+  const unsigned acc_mask = __ballot_sync(0xffffffffu, accepted);
+  if (lane == 0 && acc_mask) atomicAdd(a.n_accept, (unsigned long long)__popc(acc_mask));
+
+  // ---- stage the accepted proposal's rows -----------------------------------------
+  if (g >= a.n_groups) return;
+  uint32_t so = STG_REJECTED;
+  if (accepted) {
+    if (total == 0) so = STG_EMPTY;
+    else {
+      const int hw = stage_header_words(n_br);
+      const unsigned long long need = (unsigned long long)hw + total;
+      const unsigned long long at = atomicAdd(a.stage_ctr, need);
+      if (at + need > a.stage_cap) atomicOr(a.err, ERR_STAGE_CAPACITY);
+      else {
+        so = (uint32_t)at;
+        double *blob = a.stage + at;
+        uint16_t *cnt = reinterpret_cast<uint16_t *>(blob);
+        for (int bi = 0; bi < 4*hw; ++bi) cnt[bi] = bi < n_br ? pn[bi + 1] : 0;
+        for (int k = 0; k < total; ++k) blob[hw + k] = pr.pj[k];
+      }
+    }
+  }
+  a.stage_off[g] = so;
+}
+
+// ---- CSR re-compaction ------------------------------------------------------------------
 constexpr unsigned long long FLAG_AGG = 1ull << 32, FLAG_INC = 2ull << 32;
 
 __device__ __forceinline__ unsigned long long
@@ -65,75 +156,29 @@ tile_base(unsigned long long *desc, uint32_t tile, uint32_t epoch, uint32_t tota
   return base;
 }
 
-template <int MAXN, int MAXJ>
+
 __global__ void __launch_bounds__(MH_THREADS)
-mh_pass_kernel(const PassArgs a) {
+csr_rebuild_kernel(const PassArgs a) {
   extern __shared__ uint32_t s_len[];            // [n_branches][MH_THREADS]
-  __shared__ ModelParams s_mp;
-  __shared__ CtxTables s_tb;
   __shared__ uint32_t s_tile;
   __shared__ int s_fail;
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int n_br = a.tree.n_nodes - 1;
   if (t == 0) {
-    s_tile = atomicAdd(a.ticket, 1u) - a.ticket_base;
+    s_tile = atomicAdd(a.ticket, 1u) - a.ticket_base;   // tile order = scheduling order
     s_fail = 0;
-    s_mp = a.mp;
   }
-  fill_tables(a.mp, s_tb, t);
   __syncthreads();
   const uint32_t tile = s_tile;
   const uint64_t g = (uint64_t)tile*MH_THREADS + t;     // group of sites 3g..3g+2
-  const uint64_t s0 = 3*g;
-  const uint64_t st = s0 + a.colour;                    // the group's target site
-  const int64_t gsite = a.global0 + (int64_t)st;
+  const uint64_t s0 = 3*g, st = s0 + a.colour;
+  const uint32_t so = g < a.n_groups ? a.stage_off[g] : STG_REJECTED;
+  const bool accepted = so != STG_REJECTED;
+  const int hw = stage_header_words(n_br);
+  const uint16_t *cnt = so < STG_EMPTY ? reinterpret_cast<const uint16_t *>(a.stage + so) : nullptr;
+  const double *pj = so < STG_EMPTY ? a.stage + so + hw : nullptr;
 
-  // ---- phase 1: the update -------------------------------------------------------
-  constexpr int PB = 16, QCAP = 8;
-  FlatScratch<MAXN, PB, QCAP> S;
-  double pj_local[MAXJ];
-  uint16_t pn[MAXN];
-  uint8_t pend[MAXN];
-  Proposal pr; pr.pj = pj_local; pr.cap = MAXJ; pr.pn = pn; pr.pend = pend;
-  int accepted = 0, total = 0;
-  {
-    const bool active = st >= a.upd_lo && st < a.upd_hi && gsite >= 1 && gsite + 1 < (int64_t)a.n_global;
-    SiteCtx c; c.pv = a.in; c.state = a.state; c.W = a.W; c.tree = a.tree; c.site = st;
-    int r = mh_site_flat<MAXN, PB, QCAP>(active, s_mp, s_tb, c, a.state, a.tri_llh, a.seed, a.sweep,
-                                         (uint64_t)gsite, a.n_global, S, pr, total);
-    // -3: interval stack too small -- a property of the neighbours' rows only, so switching
-    // to the generic per-branch routine here is unbiased (rare; runs divergently)
-    const bool generic = r == -3;
-    if (generic)
-      r = mh_site(s_mp, c, a.state, a.tri_llh, a.seed, a.sweep, (uint64_t)gsite, a.n_global,
-                  S.q, pr, total);
-    // -1: proposal longer than the per-thread buffer: rerun with a global scratch slot and
-    // the same streams (=> the same proposal).  The flat routine is warp-synchronous, so the
-    // whole warp re-enters it with only the overflowing lanes active.
-    if (__any_sync(0xffffffffu, r == -1)) {
-      const bool again = r == -1;
-      if (again) {
-        const uint32_t slot = atomicAdd(a.scratch_ctr, 1u);
-        if (slot >= a.scratch_slots) { atomicOr(a.err, ERR_SCRATCH_SLOTS); r = 0; }
-        else { pr.pj = a.scratch + (uint64_t)slot*a.scratch_cap; pr.cap = (int)a.scratch_cap; }
-      }
-      const bool redo = again && r == -1;
-      const int r2 = mh_site_flat<MAXN, PB, QCAP>(redo && !generic, s_mp, s_tb, c, a.state, a.tri_llh,
-                                                  a.seed, a.sweep, (uint64_t)gsite, a.n_global, S, pr, total);
-      if (redo && !generic) r = r2;
-      if (redo && generic)
-        r = mh_site(s_mp, c, a.state, a.tri_llh, a.seed, a.sweep, (uint64_t)gsite, a.n_global,
-                    S.q, pr, total);
-      if (r == -1) { atomicOr(a.err, ERR_SCRATCH_SIZE); r = 0; }
-    }
-    if (r == -2) { atomicOr(a.err, ERR_SAMPLER_STUCK); r = 0; }
-    if (r < 0) r = 0;
-    accepted = r;
-  }
-  const unsigned acc_mask = __ballot_sync(0xffffffffu, accepted);
-  if (lane == 0 && acc_mask) atomicAdd(a.n_accept, (unsigned long long)__popc(acc_mask));
-
-  // ---- phase 2: new row lengths of the group's OWNED sites, summed per thread -----
+  // ---- new row lengths of the group's OWNED sites, summed per thread ----------------
   // CSR row index of local site s is s - own_lo; the group's owned sites are the
   // contiguous range [r0, r1) of it (empty for a group that lies in a halo).
   const uint64_t own_lo = a.in.own_lo, own_hi = a.in.own_hi, n_own = own_hi - own_lo;
@@ -145,13 +190,13 @@ mh_pass_kernel(const PassArgs a) {
     if (has_rows) {
       const uint32_t *o = a.in.off + (uint64_t)bi*a.in.off_pitch;
       sum = o[r1] - o[r0];
-      if (accepted) sum = sum - (o[st - own_lo + 1] - o[st - own_lo]) + pn[bi + 1];
+      if (accepted) sum = sum - (o[st - own_lo + 1] - o[st - own_lo]) + (cnt ? cnt[bi] : 0u);
     }
     s_len[bi*MH_THREADS + t] = sum;
   }
   __syncthreads();
 
-  // ---- phase 3: per-branch tile scan + chained look-back ------------------------
+  // ---- per-branch tile scan + chained look-back -------------------------------------
   for (int bi = warp; bi < n_br; bi += MH_THREADS/32) {
     uint32_t *row = s_len + bi*MH_THREADS;
     uint32_t v[MH_THREADS/32], mine = 0;
@@ -178,7 +223,7 @@ mh_pass_kernel(const PassArgs a) {
   __syncthreads();
   if (s_fail || !has_rows) return;
 
-  // ---- phase 4: write the rebuilt rows ---------------------------------------------
+  // ---- write the rebuilt rows ------------------------------------------------------------
   int poff = 0;
   for (int bi = 0; bi < n_br; ++bi) {
     const uint32_t *o = a.in.off + (uint64_t)bi*a.in.off_pitch;
@@ -186,12 +231,12 @@ mh_pass_kernel(const PassArgs a) {
     const double *src_base = a.in.jmp + a.in.jbase[bi];
     double *dst_base = a.jmp_out + a.in.jbase[bi];
     uint32_t w = s_len[bi*MH_THREADS + t];
+    const int n_new = cnt ? cnt[bi] : 0;
     for (uint64_t r = r0; r < r1; ++r) {
       oo[r] = w;
       if (accepted && r + own_lo == st) {
-        const int n = pn[bi + 1];
-        for (int k = 0; k < n; ++k) dst_base[w + k] = pr.pj[poff + k];
-        w += n;
+        for (int k = 0; k < n_new; ++k) dst_base[w + k] = pj[poff + k];
+        w += n_new;
       }
       else {
         const uint32_t b = o[r], e = o[r + 1];
@@ -199,7 +244,7 @@ mh_pass_kernel(const PassArgs a) {
         w += e - b;
       }
     }
-    poff += pn[bi + 1];
+    poff += n_new;
   }
 }
 
@@ -212,20 +257,25 @@ mh_pass_smem_bytes(int n_nodes) {
 
 template <int MAXN, int MAXJ>
 static void
-launch_t(const PassArgs &a, cudaStream_t st) {
-  const size_t smem = mh_pass_smem_bytes(a.tree.n_nodes);
-  cudaFuncSetAttribute(mh_pass_kernel<MAXN, MAXJ>,
-                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  mh_pass_kernel<MAXN, MAXJ><<<a.n_tiles, MH_THREADS, smem, st>>>(a);
+launch_update_t(const PassArgs &a, cudaStream_t st) {
+  const unsigned blocks = (unsigned)((a.n_groups + MH_THREADS - 1)/MH_THREADS);
+  mh_update_kernel<MAXN, MAXJ><<<blocks, MH_THREADS, 0, st>>>(a);
 }
 
 void
 launch_mh_pass(const PassArgs &a, cudaStream_t st) {
   const int n = a.tree.n_nodes;
-  if (n <= 8) launch_t<8, 16>(a, st);
-  else if (n <= 16) launch_t<16, 32>(a, st);
-  else if (n <= 64) launch_t<64, 64>(a, st);
-  else launch_t<256, 128>(a, st);
+  if (n <= 8) launch_update_t<8, 16>(a, st);
+  else if (n <= 16) launch_update_t<16, 32>(a, st);
+  else if (n <= 64) launch_update_t<64, 64>(a, st);
+  else launch_update_t<256, 128>(a, st);
+}
+
+void
+launch_csr_rebuild(const PassArgs &a, cudaStream_t st) {
+  const size_t smem = mh_pass_smem_bytes(a.tree.n_nodes);
+  cudaFuncSetAttribute(csr_rebuild_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  csr_rebuild_kernel<<<a.n_tiles, MH_THREADS, smem, st>>>(a);
 }
 
 }  // namespace epv

@@ -173,12 +173,14 @@ mh_site_flat(bool active, const ModelParams &mp, const CtxTables &tb, const Site
       const double P00 = tb.pi1[ctx] + tb.pi0[ctx]*h, P11 = tb.pi0[ctx] + tb.pi1[ctx]*h;
       const double to0 = prev ? 1.0 - P11 : P00, to1 = prev ? P11 : 1.0 - P00;
       const double a0 = to0*nx0, a1 = to1*nx1;
-      const int e = rng.uniform()*(a0 + a1) > a0;          // end state of the interval
+      double u_end, u_jump;
+      rng.uniform2(u_end, u_jump);
+      const int e = u_end*(a0 + a1) > a0;                  // end state of the interval
       bool need_jumps = e != prev;
       if (!need_jumps) {
         // P(no jump | start == end) = exp(-r_prev len) / P(prev -> prev)
         const double ea = exp(-len*(prev ? mp.rate[ctx | 2] : mp.rate[ctx]));
-        need_jumps = !(rng.uniform()*(prev ? P11 : P00) < ea);
+        need_jumps = !(u_jump*(prev ? P11 : P00) < ea);
       }
       if (need_jumps) {
         if (qn == QCAP) total = drain_queue<QCAP>(mp, S.queue, qn, rng, pr, total);
