@@ -9,7 +9,7 @@ over one GPU's block of sites.  Updates per step = (L+B) * (n_sites-2) * n_branc
   value : paths already resident in HBM when the timed region starts (epv_run_mcmc)
   e2e   : the same call with HOST buffers -- pinned host paths uploaded, E-step run,
           paths + J/D read back, all inside the timed region
-  roofline : the colour-pass kernel (mh_pass_kernel), algorithmic bytes per launch
+  roofline : the colour-pass update kernel (mh_update_kernel), algorithmic bytes per launch
           = (4/3) * n_sites * n_branches * (4 + 1/8 + 8*jbar)   
           over its mean launch time from CUDA events around every launch
   cpu_baseline : the unmodified reference (oracle/_ref) on one host core, bounded sample
@@ -265,6 +265,7 @@ def main():
     clk = clocks.stop()
     ms = e0.elapsed_time(e1)
     mh_ms, mh_launches = ctx.mh_kernel_time(reset=True)
+    rebuild_ms = ctx.rebuild_kernel_time()
     ctx.enable_kernel_timing(False)
     launches = ctx.launch_count() - launches0
     jc = ctx.jump_counts()
@@ -319,10 +320,12 @@ def main():
     avg_launch_ms = mh_ms / max(1, mh_launches)
     achieved = bytes_per_launch / (avg_launch_ms * 1e-3) / 1e9 if avg_launch_ms > 0 else 0.0
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None, "kernel": "mh_pass_kernel",
+                "frac": achieved / peak, "traffic": None, "kernel": "mh_update_kernel",
                 "peak_source": peak_src, "avg_launch_ms": avg_launch_ms, "launches_timed": mh_launches,
                 "algorithmic_bytes_per_launch": bytes_per_launch, "jumps_per_row": jbar,
-                "kernel_share_of_step": mh_ms / ms if ms > 0 else None}
+                "kernel_share_of_step": mh_ms / ms if ms > 0 else None,
+                "rebuild_kernel_avg_ms": rebuild_ms / max(1, mh_launches),
+                "rebuild_kernel_share_of_step": rebuild_ms / ms if ms > 0 else None}
 
     # ---- CPU baseline (rank 0, N=1 only) ---------------------------------------------------
     cpu_baseline = None

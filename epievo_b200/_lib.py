@@ -8,7 +8,8 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libepievo_b200.so")
+# EPIEVO_B200_LIB: A/B-test another build of the same library (tools/build_variants.sh)
+LIB_PATH = os.environ.get("EPIEVO_B200_LIB") or os.path.join(HERE, "libepievo_b200.so")
 
 dp = C.POINTER(C.c_double)
 u64p = C.POINTER(C.c_uint64)
@@ -55,6 +56,7 @@ SIGNATURES = {
     "epv_set_one_change": (None, [dp, u64, dp]),
     "epv_launch_count": (u64, [ctx_p]),
     "epv_mh_kernel_time": (C.c_int, [ctx_p, C.c_int, dp, u64p]),
+    "epv_rebuild_kernel_time": (C.c_int, [ctx_p, dp]),
     "epv_enable_kernel_timing": (C.c_int, [ctx_p, C.c_int]),
     "epv_jump_counts": (C.c_int, [ctx_p, u64p]),
 }

@@ -77,7 +77,7 @@ int epv_create(epv_ctx **out, int device) {
     && cudaMallocHost(&c->h_mail, 4096*sizeof(unsigned long long)) == cudaSuccess
     && cudaMalloc(&c->d_scratch, (size_t)c->scratch_slots*c->scratch_cap*sizeof(double)) == cudaSuccess
     && cudaEventCreate(&c->ev0) == cudaSuccess && cudaEventCreate(&c->ev1) == cudaSuccess;
-  for (int k = 0; ok && k < 2*epv_ctx::EV_RING; ++k)
+  for (int k = 0; ok && k < 3*epv_ctx::EV_RING; ++k)
     ok = cudaEventCreate(&c->ev_ring[k]) == cudaSuccess;
   if (ok) {
     c->stream = c->own_stream;
@@ -106,7 +106,7 @@ void epv_destroy(epv_ctx *c) {
   cudaFree(c->d_scratch); cudaFree(c->d_out9); cudaFree(c->d_mail); cudaFreeHost(c->h_mail);
   cudaFree(c->d_J); cudaFree(c->d_D); cudaFree(c->d_Jsum); cudaFree(c->d_Dsum); cudaFree(c->d_ss);
   cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1);
-  for (int k = 0; k < 2*epv_ctx::EV_RING; ++k) if (c->ev_ring[k]) cudaEventDestroy(c->ev_ring[k]);
+  for (int k = 0; k < 3*epv_ctx::EV_RING; ++k) if (c->ev_ring[k]) cudaEventDestroy(c->ev_ring[k]);
   cudaStreamDestroy(c->own_stream);
   delete c;
 }

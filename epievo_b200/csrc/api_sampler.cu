@@ -32,10 +32,11 @@ void interior(const epv_ctx *c, uint64_t &lo, uint64_t &hi) {
 // Resolve the pending (start, stop) event pairs of the colour-pass launches.
 void drain_timing(epv_ctx *c) {
   if (!c->ev_pending) return;
-  cudaEventSynchronize(c->ev_ring[2*c->ev_pending - 1]);
+  cudaEventSynchronize(c->ev_ring[3*c->ev_pending - 1]);
   for (int k = 0; k < c->ev_pending; ++k) {
     float ms = 0.f;
-    if (cudaEventElapsedTime(&ms, c->ev_ring[2*k], c->ev_ring[2*k + 1]) == cudaSuccess) c->mh_ms += ms;
+    if (cudaEventElapsedTime(&ms, c->ev_ring[3*k], c->ev_ring[3*k + 1]) == cudaSuccess) c->mh_ms += ms;
+    if (cudaEventElapsedTime(&ms, c->ev_ring[3*k + 1], c->ev_ring[3*k + 2]) == cudaSuccess) c->rebuild_ms += ms;
   }
   c->ev_pending = 0;
 }
@@ -72,14 +73,17 @@ int one_pass(epv_ctx *c, int colour, uint64_t seed, uint32_t sweep) {
   EPV_CUDA(c, cudaMemsetAsync(c->d_stg_ctr, 0, sizeof(unsigned long long), c->stream));
   if (c->timing) {
     if (c->ev_pending == epv_ctx::EV_RING) drain_timing(c);
-    cudaEventRecord(c->ev_ring[2*c->ev_pending], c->stream);
+    cudaEventRecord(c->ev_ring[3*c->ev_pending], c->stream);
   }
   launch_mh_pass(a, c->stream);
   if (c->timing) {
-    cudaEventRecord(c->ev_ring[2*c->ev_pending + 1], c->stream);
-    ++c->ev_pending;
+    cudaEventRecord(c->ev_ring[3*c->ev_pending + 1], c->stream);
   }
   launch_csr_rebuild(a, c->stream);
+  if (c->timing) {
+    cudaEventRecord(c->ev_ring[3*c->ev_pending + 2], c->stream);
+    ++c->ev_pending;
+  }
   c->launches += 2; ++c->mh_launches;
   c->ticket_base += c->n_tiles;
   c->cur ^= 1;
@@ -244,13 +248,20 @@ int epv_enable_kernel_timing(epv_ctx *c, int on) {
   return 0;
 }
 
+int epv_rebuild_kernel_time(epv_ctx *c, double *ms) {
+  if (!c || !ms) return 1;
+  *ms = c->last_rebuild_ms;
+  return 0;
+}
+
 int epv_mh_kernel_time(epv_ctx *c, int reset, double *ms, uint64_t *launches) {
   if (!c) return 1;
   cudaSetDevice(c->device);
   drain_timing(c);
   if (ms) *ms = c->mh_ms;
+  c->last_rebuild_ms = c->rebuild_ms;
   if (launches) *launches = c->mh_launches;
-  if (reset) { c->mh_ms = 0.0; c->mh_launches = 0; }
+  if (reset) { c->mh_ms = 0.0; c->rebuild_ms = 0.0; c->mh_launches = 0; }
   return 0;
 }
 

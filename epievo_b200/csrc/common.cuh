@@ -46,7 +46,8 @@ struct PathView {
   const double *jmp;
   const uint64_t *jbase;    // [n_branches] start of each branch's slice of jmp
   uint64_t off_pitch;
-  uint64_t own_lo, own_hi;
+  uint64_t own_lo, own_hi;  // owned local sites [own_lo, own_hi) of n_local
+  uint64_t n_local;
   const uint16_t *hcnt;
   const double *hjmp;
   int n_br;

@@ -68,17 +68,17 @@ struct epv_ctx {
   // instrumentation
   uint64_t launches = 0, mh_launches = 0;
   bool timing = false;
-  double mh_ms = 0.0;
+  double mh_ms = 0.0, rebuild_ms = 0.0, last_rebuild_ms = 0.0;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   // ring of (start, stop) event pairs around the colour-pass launches; resolved
   // lazily (after the per-sweep stream sync) so timing never stalls the stream
   static constexpr int EV_RING = 96;
-  cudaEvent_t ev_ring[2*EV_RING] = {};
+  cudaEvent_t ev_ring[3*EV_RING] = {};       // (before update, between, after rebuild)
   int ev_pending = 0;
 
   epv::PathView view(int which) const {
     epv::PathView v; v.off = d_off[which]; v.jmp = d_jmp[which]; v.jbase = d_jbase;
-    v.off_pitch = off_pitch; v.own_lo = halo_lo; v.own_hi = n_sites - halo_hi;
+    v.off_pitch = off_pitch; v.own_lo = halo_lo; v.own_hi = n_sites - halo_hi; v.n_local = n_sites;
     v.hcnt = d_hcnt; v.hjmp = d_hjmp; v.n_br = n_nodes - 1; return v;
   }
   epv::TreeDev tree() const {

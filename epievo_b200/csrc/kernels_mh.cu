@@ -28,8 +28,12 @@ constexpr uint32_t STG_REJECTED = 0xffffffffu, STG_EMPTY = 0xfffffffeu;
 
 __device__ __forceinline__ int stage_header_words(int n_br) { return (n_br + 3) >> 2; }
 
-template <int MAXN, int MAXJ>
-__global__ void __launch_bounds__(MH_THREADS)
+#ifndef EPV_MH_MINBLOCKS
+#define EPV_MH_MINBLOCKS 1
+#endif
+
+template <int MAXN, int MAXJ, bool HALO>
+__global__ void __launch_bounds__(MH_THREADS, EPV_MH_MINBLOCKS)
 mh_update_kernel(const PassArgs a) {
   __shared__ ModelParams s_mp;
   __shared__ CtxTables s_tb;
@@ -52,7 +56,7 @@ mh_update_kernel(const PassArgs a) {
   {
     const bool active = st >= a.upd_lo && st < a.upd_hi && gsite >= 1 && gsite + 1 < (int64_t)a.n_global;
     SiteCtx c; c.pv = a.in; c.state = a.state; c.W = a.W; c.tree = a.tree; c.site = st;
-    int r = mh_site_flat<MAXN, PB, QCAP>(active, s_mp, s_tb, c, a.state, a.tri_llh, a.seed, a.sweep,
+    int r = mh_site_flat<MAXN, PB, QCAP, HALO>(active, s_mp, s_tb, c, a.state, a.tri_llh, a.seed, a.sweep,
                                          (uint64_t)gsite, a.n_global, S, pr, total);
     // -3: interval stack too small -- a property of the neighbours' rows only, so switching
     // to the generic per-branch routine here is unbiased (rare; runs divergently)
@@ -71,7 +75,7 @@ mh_update_kernel(const PassArgs a) {
         else { pr.pj = a.scratch + (uint64_t)slot*a.scratch_cap; pr.cap = (int)a.scratch_cap; }
       }
       const bool redo = again && r == -1;
-      const int r2 = mh_site_flat<MAXN, PB, QCAP>(redo && !generic, s_mp, s_tb, c, a.state, a.tri_llh,
+      const int r2 = mh_site_flat<MAXN, PB, QCAP, HALO>(redo && !generic, s_mp, s_tb, c, a.state, a.tri_llh,
                                                   a.seed, a.sweep, (uint64_t)gsite, a.n_global, S, pr, total);
       if (redo && !generic) r = r2;
       if (redo && generic)
@@ -259,7 +263,10 @@ template <int MAXN, int MAXJ>
 static void
 launch_update_t(const PassArgs &a, cudaStream_t st) {
   const unsigned blocks = (unsigned)((a.n_groups + MH_THREADS - 1)/MH_THREADS);
-  mh_update_kernel<MAXN, MAXJ><<<blocks, MH_THREADS, 0, st>>>(a);
+  if (a.in.own_lo == 0 && a.in.own_hi == a.in.n_local)
+    mh_update_kernel<MAXN, MAXJ, false><<<blocks, MH_THREADS, 0, st>>>(a);
+  else
+    mh_update_kernel<MAXN, MAXJ, true><<<blocks, MH_THREADS, 0, st>>>(a);
 }
 
 void

@@ -36,24 +36,65 @@ fill_tables(const ModelParams &mp, CtxTables &tb, int t) {
   }
 }
 
-// Rows of sites s-1, s, s+1 on branch bi (own row: count only).
+// Init-state bit sets of sites s-2..s+2, read once per update (WORDS x 64 node bits).
+template <int WORDS>
+struct StateWin {
+  uint64_t w[5][WORDS];
+  __device__ __forceinline__ void
+  load(const uint8_t *state, int W, uint64_t s, uint64_t n_sites) {
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+#pragma unroll
+      for (int j = 0; j < WORDS; ++j) w[k][j] = 0;
+      const int64_t site = (int64_t)s + k - 2;
+      if (site >= 0 && site < (int64_t)n_sites)
+        for (int b = 0; b < W; ++b)
+          w[k][WORDS == 1 ? 0 : b >> 3] |= (uint64_t)state[(uint64_t)site*W + b] << (8*(b & 7));
+    }
+  }
+  // d = site offset relative to s (-2..2)
+  __device__ __forceinline__ int bit(int d, int node) const {
+    return (int)((w[d + 2][WORDS == 1 ? 0 : node >> 6] >> (node & 63)) & 1u);
+  }
+};
+
+// Jump times and count of one row; HALO=false skips the halo-store branch (single-GPU
+// contexts own every local site).
+template <bool HALO>
 __device__ __forceinline__ void
-load_lmr(const PathView &pv, const uint8_t *state, int W, int bi, uint64_t site,
+row_data(const PathView &pv, int bi, uint64_t site, const double *&ptr, int &n) {
+  if (!HALO || (site >= pv.own_lo && site < pv.own_hi)) {
+    const uint32_t *o = pv.off + (uint64_t)bi*pv.off_pitch + (site - pv.own_lo);
+    const uint32_t a = o[0], b = o[1];
+    ptr = pv.jmp + pv.jbase[bi] + a; n = (int)(b - a);
+  }
+  else {
+    const int slot = site < pv.own_lo ? (int)site : HALO_W + (int)(site - pv.own_hi);
+    n = pv.hcnt[slot*pv.n_br + bi];
+    ptr = pv.hjmp + (size_t)(slot*pv.n_br + bi)*HALO_K;
+  }
+}
+
+// Rows of sites s-1, s, s+1 on branch bi (own row: count only).
+template <bool HALO, int WORDS>
+__device__ __forceinline__ void
+load_lmr(const PathView &pv, const StateWin<WORDS> &sw, int bi, uint64_t site,
          Row &L, Row &R, int &own_n) {
-  if (site - 1 >= pv.own_lo && site + 1 < pv.own_hi) {
+  L.init = sw.bit(-1, bi + 1);
+  R.init = sw.bit(1, bi + 1);
+  if (!HALO || (site - 1 >= pv.own_lo && site + 1 < pv.own_hi)) {
     const uint32_t *o = pv.off + (uint64_t)bi*pv.off_pitch + (site - 1 - pv.own_lo);
     const uint32_t o0 = o[0], o1 = o[1], o2 = o[2], o3 = o[3];
     const double *base = pv.jmp + pv.jbase[bi];
     L.ptr = base + o0; L.n = (int)(o1 - o0);
     own_n = (int)(o2 - o1);
     R.ptr = base + o2; R.n = (int)(o3 - o2);
-    L.init = state_bit(state, W, site - 1, bi + 1);
-    R.init = state_bit(state, W, site + 1, bi + 1);
   }
   else {
-    L = load_row(pv, state, W, bi, site - 1);
-    R = load_row(pv, state, W, bi, site + 1);
-    own_n = load_row(pv, state, W, bi, site).n;
+    const double *dummy;
+    row_data<true>(pv, bi, site - 1, L.ptr, L.n);
+    row_data<true>(pv, bi, site + 1, R.ptr, R.n);
+    row_data<true>(pv, bi, site, dummy, own_n);
   }
 }
 
@@ -96,7 +137,7 @@ drain_queue(const ModelParams &mp, QItem *queue, int &qn, Philox &rng, Proposal 
 // no early returns (a failing lane records its status and idles).  Without this the
 // compiler leaves lanes that left a loop at different iterations diverged for the rest
 // of the function (measured: 2-4 active lanes per instruction).
-template <int MAXN, int PB, int QCAP>
+template <int MAXN, int PB, int QCAP, bool HALO>
 __device__ __forceinline__ int
 mh_site_flat(bool active, const ModelParams &mp, const CtxTables &tb, const SiteCtx &c,
              uint8_t *state_rw, double *tri_llh, uint64_t seed, uint32_t sweep, uint64_t gsite,
@@ -106,6 +147,8 @@ mh_site_flat(bool active, const ModelParams &mp, const CtxTables &tb, const Site
   const uint64_t s = c.site;
   double *q = S.q;
   int status = 1;                       // becomes <0 on failure; the lane then idles
+  StateWin<(MAXN + 63)/64> sw;
+  if (active) sw.load(c.state, c.W, s, c.pv.n_local);
 
   // ---- 1. upward pruning, flat over (branch, interval) ----------------------------
   for (int v = 0; v < n_nodes; ++v) { q[2*v] = 1.0; q[2*v + 1] = 1.0; pr.pn[v] = 0; }
@@ -119,10 +162,10 @@ mh_site_flat(bool active, const ModelParams &mp, const CtxTables &tb, const Site
       if (v < 1) continue;
       if (need_init) {
         Row L, R; int own_n;
-        load_lmr(c.pv, c.state, c.W, v - 1, s, L, R, own_n);
+        load_lmr<HALO>(c.pv, sw, v - 1, s, L, R, own_n);
         m.start(L, R, c.tree.branch[v]);
         if (c.tree.subtree[v] == 1) {
-          const int leaf = state_bit(c.state, c.W, s, v) ^ (own_n & 1);
+          const int leaf = sw.bit(0, v) ^ (own_n & 1);
           p0 = leaf ? 0.0 : 1.0; p1 = leaf ? 1.0 : 0.0;
           q[2*v] = p0; q[2*v + 1] = p1;
         }
@@ -148,7 +191,7 @@ mh_site_flat(bool active, const ModelParams &mp, const CtxTables &tb, const Site
 
   // ---- 2. downward pass, flat over (branch, interval) -----------------------------
   Philox rng; rng.init(seed, sweep, gsite, 1u);
-  pr.pend[0] = active ? (uint8_t)state_bit(c.state, c.W, s, 1) : 0;
+  pr.pend[0] = active ? (uint8_t)sw.bit(0, 1) : 0;
   int total = 0, qn = 0;
   {
     int v = (active && status > 0) ? 1 : n_nodes, prev = 0, i = 0;
@@ -159,7 +202,7 @@ mh_site_flat(bool active, const ModelParams &mp, const CtxTables &tb, const Site
       if (v >= n_nodes) continue;
       if (need_init) {
         Row L, R; int own_n;
-        load_lmr(c.pv, c.state, c.W, v - 1, s, L, R, own_n);
+        load_lmr<HALO>(c.pv, sw, v - 1, s, L, R, own_n);
         m.start(L, R, c.tree.branch[v]);
         prev = pr.pend[c.tree.parent[v]];
         passed = 0.0; i = 0; need_init = false;
@@ -207,10 +250,10 @@ mh_site_flat(bool active, const ModelParams &mp, const CtxTables &tb, const Site
   double xl = 0.0, xm = 0.0, xr = 0.0;
   if (live) {
     const int sm = pr.pend[0];
-    const int sl1 = state_bit(c.state, c.W, s - 1, 1), sr1 = state_bit(c.state, c.W, s + 1, 1);
+    const int sl1 = sw.bit(-1, 1), sr1 = sw.bit(1, 1);
     xm = mp.T[sl1*2 + sm]*mp.T[sm*2 + sr1];
-    xl = do_l ? mp.T[state_bit(c.state, c.W, s - 2, 1)*2 + sl1]*mp.T[sl1*2 + sm] : l_old;
-    xr = do_r ? mp.T[sm*2 + sr1]*mp.T[sr1*2 + state_bit(c.state, c.W, s + 2, 1)] : r_old;
+    xl = do_l ? mp.T[sw.bit(-2, 1)*2 + sl1]*mp.T[sl1*2 + sm] : l_old;
+    xr = do_r ? mp.T[sm*2 + sr1]*mp.T[sr1*2 + sw.bit(2, 1)] : r_old;
   }
   {
     const double INF = __longlong_as_double(0x7ff0000000000000LL);
@@ -224,10 +267,12 @@ mh_site_flat(bool active, const ModelParams &mp, const CtxTables &tb, const Site
       if (v >= n_nodes) continue;
       if (need_init) {
         const int bi = v - 1;
-        B = load_row(c.pv, c.state, c.W, bi, s - 1);
-        C = load_row(c.pv, c.state, c.W, bi, s + 1);
-        if (do_l) A = load_row(c.pv, c.state, c.W, bi, s - 2); else { A.n = 0; A.init = 0; A.ptr = B.ptr; }
-        if (do_r) E = load_row(c.pv, c.state, c.W, bi, s + 2); else { E.n = 0; E.init = 0; E.ptr = C.ptr; }
+        row_data<HALO>(c.pv, bi, s - 1, B.ptr, B.n); B.init = sw.bit(-1, v);
+        row_data<HALO>(c.pv, bi, s + 1, C.ptr, C.n); C.init = sw.bit(1, v);
+        if (do_l) { row_data<HALO>(c.pv, bi, s - 2, A.ptr, A.n); A.init = sw.bit(-2, v); }
+        else { A.n = 0; A.init = 0; A.ptr = B.ptr; }
+        if (do_r) { row_data<HALO>(c.pv, bi, s + 2, E.ptr, E.n); E.init = sw.bit(2, v); }
+        else { E.n = 0; E.init = 0; E.ptr = C.ptr; }
         P.ptr = pr.pj + poff; P.n = pr.pn[v]; P.init = pr.pend[c.tree.parent[v]];
         poff += P.n;
         iA = iB = iP = iC = iE = 0;

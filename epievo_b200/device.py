@@ -215,3 +215,8 @@ class Context:
         ms, n = C.c_double(), C.c_uint64()
         self._ck(self.lib.epv_mh_kernel_time(self.h, int(reset), C.byref(ms), C.byref(n)))
         return ms.value, n.value
+
+    def rebuild_kernel_time(self) -> float:
+        ms = C.c_double()
+        self._ck(self.lib.epv_rebuild_kernel_time(self.h, C.byref(ms)))
+        return ms.value

@@ -177,8 +177,11 @@ void epv_set_one_change(double *rates, uint64_t n_nodes, double *branches);
 /* Kernel launches issued by this context since creation (bench "gpu_launches"). */
 uint64_t epv_launch_count(const epv_ctx *ctx);
 /* Device time (ms, CUDA events on the context's stream) and launch count of the
- * colour-pass kernel accumulated since the last call with reset != 0. */
+ * colour-pass update kernel (mh_update_kernel) accumulated since the last call with
+ * reset != 0; epv_rebuild_kernel_time returns the csr_rebuild_kernel time accumulated
+ * over the same launches, as of the last epv_mh_kernel_time call. */
 int epv_mh_kernel_time(epv_ctx *ctx, int reset, double *ms, uint64_t *launches);
+int epv_rebuild_kernel_time(epv_ctx *ctx, double *ms);
 int epv_enable_kernel_timing(epv_ctx *ctx, int on);
 /* Total jumps currently stored, per node ([n_nodes], entry 0 zero). */
 int epv_jump_counts(epv_ctx *ctx, uint64_t *per_node);
