@@ -6,6 +6,8 @@ namespace epv {
 
 constexpr int MH_THREADS = 128;                 // groups (of 3 sites) per tile
 constexpr int MH_TILE_SITES = 3*MH_THREADS;
+constexpr int RB_THREADS = 256;                 // rebuild kernel: 4 CSR rows per thread
+constexpr int RB_TILE_ROWS = 4*RB_THREADS;
 
 struct PassArgs {
   ModelParams mp;

@@ -161,9 +161,12 @@ tile_base(unsigned long long *desc, uint32_t tile, uint32_t epoch, uint32_t tota
 }
 
 
-__global__ void __launch_bounds__(MH_THREADS)
+// Thread t of tile k owns the 4 consecutive CSR rows R = 4*(k*RB_THREADS + t) .. R+3 of
+// every branch (offsets move as one 16-byte vector).  Rows whose site has the pass's colour
+// take their new length / jump times from the staging blob when the update was accepted.
+__global__ void __launch_bounds__(RB_THREADS)
 csr_rebuild_kernel(const PassArgs a) {
-  extern __shared__ uint32_t s_len[];            // [n_branches][MH_THREADS]
+  extern __shared__ uint32_t s_len[];            // [n_branches][RB_THREADS]
   __shared__ uint32_t s_tile;
   __shared__ int s_fail;
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
@@ -174,38 +177,56 @@ csr_rebuild_kernel(const PassArgs a) {
   }
   __syncthreads();
   const uint32_t tile = s_tile;
-  const uint64_t g = (uint64_t)tile*MH_THREADS + t;     // group of sites 3g..3g+2
-  const uint64_t s0 = 3*g, st = s0 + a.colour;
-  const uint32_t so = g < a.n_groups ? a.stage_off[g] : STG_REJECTED;
-  const bool accepted = so != STG_REJECTED;
+  const uint64_t own_lo = a.in.own_lo, n_own = a.in.own_hi - own_lo;
+  const uint64_t R = 4*((uint64_t)tile*RB_THREADS + t);
   const int hw = stage_header_words(n_br);
-  const uint16_t *cnt = so < STG_EMPTY ? reinterpret_cast<const uint16_t *>(a.stage + so) : nullptr;
-  const double *pj = so < STG_EMPTY ? a.stage + so + hw : nullptr;
 
-  // ---- new row lengths of the group's OWNED sites, summed per thread ----------------
-  // CSR row index of local site s is s - own_lo; the group's owned sites are the
-  // contiguous range [r0, r1) of it (empty for a group that lies in a halo).
-  const uint64_t own_lo = a.in.own_lo, own_hi = a.in.own_hi, n_own = own_hi - own_lo;
-  const uint64_t g_lo = max(s0, own_lo), g_hi = min(s0 + 3, own_hi);
-  const bool has_rows = g_lo < g_hi;
-  const uint64_t r0 = has_rows ? g_lo - own_lo : 0, r1 = has_rows ? g_hi - own_lo : 0;
+  // the (at most two) rows of the quad whose site has this pass's colour
+  int tk[2] = {-1, -1};
+  const uint16_t *tcnt[2] = {nullptr, nullptr};
+  const double *tpj[2] = {nullptr, nullptr};
+  bool tacc[2] = {false, false};
+  {
+    const int k0 = (int)((a.colour + 3 - (int)((R + own_lo) % 3)) % 3);
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int k = k0 + 3*j;
+      if (k < 4 && R + k < n_own) {
+        const uint32_t so = a.stage_off[(R + k + own_lo)/3];
+        tk[j] = k;
+        tacc[j] = so != STG_REJECTED;
+        if (so < STG_EMPTY) { tcnt[j] = reinterpret_cast<const uint16_t *>(a.stage + so); tpj[j] = a.stage + so + hw; }
+      }
+    }
+  }
+
+  // ---- new row lengths of the quad, summed per thread -------------------------------
   for (int bi = 0; bi < n_br; ++bi) {
     uint32_t sum = 0;
-    if (has_rows) {
-      const uint32_t *o = a.in.off + (uint64_t)bi*a.in.off_pitch;
-      sum = o[r1] - o[r0];
-      if (accepted) sum = sum - (o[st - own_lo + 1] - o[st - own_lo]) + (cnt ? cnt[bi] : 0u);
+    if (R < n_own) {
+      const uint32_t *o = a.in.off + (uint64_t)bi*a.in.off_pitch + R;
+      const uint4 q = *reinterpret_cast<const uint4 *>(o);
+      const uint32_t e = o[4];
+      uint32_t len[4] = {q.y - q.x, q.z - q.y, q.w - q.z, e - q.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        if (R + k >= n_own) len[k] = 0;
+#pragma unroll
+        for (int j = 0; j < 2; ++j) if (tk[j] == k && tacc[j]) len[k] = tcnt[j] ? tcnt[j][bi] : 0u;
+        sum += len[k];
+      }
     }
-    s_len[bi*MH_THREADS + t] = sum;
+    s_len[bi*RB_THREADS + t] = sum;
   }
   __syncthreads();
 
   // ---- per-branch tile scan + chained look-back -------------------------------------
-  for (int bi = warp; bi < n_br; bi += MH_THREADS/32) {
-    uint32_t *row = s_len + bi*MH_THREADS;
-    uint32_t v[MH_THREADS/32], mine = 0;
+  constexpr int PER = RB_THREADS/32;
+  for (int bi = warp; bi < n_br; bi += PER) {
+    uint32_t *row = s_len + bi*RB_THREADS;
+    uint32_t v[PER], mine = 0;
 #pragma unroll
-    for (int k = 0; k < MH_THREADS/32; ++k) { v[k] = row[lane*(MH_THREADS/32) + k]; mine += v[k]; }
+    for (int k = 0; k < PER; ++k) { v[k] = row[lane*PER + k]; mine += v[k]; }
     uint32_t incl = mine;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -220,35 +241,44 @@ csr_rebuild_kernel(const PassArgs a) {
     }
     uint32_t run = base + incl - mine;
 #pragma unroll
-    for (int k = 0; k < MH_THREADS/32; ++k) { row[lane*(MH_THREADS/32) + k] = run; run += v[k]; }
-    if (tile == a.n_tiles - 1 && lane == 31)
-      a.off_out[(uint64_t)bi*a.in.off_pitch + n_own] = base + tot;
+    for (int k = 0; k < PER; ++k) { row[lane*PER + k] = run; run += v[k]; }
   }
   __syncthreads();
-  if (s_fail || !has_rows) return;
+  if (s_fail || R > n_own) return;
 
   // ---- write the rebuilt rows ------------------------------------------------------------
-  int poff = 0;
+  int poff[2] = {0, 0};
   for (int bi = 0; bi < n_br; ++bi) {
-    const uint32_t *o = a.in.off + (uint64_t)bi*a.in.off_pitch;
-    uint32_t *oo = a.off_out + (uint64_t)bi*a.in.off_pitch;
+    const uint32_t *o = a.in.off + (uint64_t)bi*a.in.off_pitch + R;
     const double *src_base = a.in.jmp + a.in.jbase[bi];
     double *dst_base = a.jmp_out + a.in.jbase[bi];
-    uint32_t w = s_len[bi*MH_THREADS + t];
-    const int n_new = cnt ? cnt[bi] : 0;
-    for (uint64_t r = r0; r < r1; ++r) {
-      oo[r] = w;
-      if (accepted && r + own_lo == st) {
-        for (int k = 0; k < n_new; ++k) dst_base[w + k] = pj[poff + k];
-        w += n_new;
-      }
-      else {
-        const uint32_t b = o[r], e = o[r + 1];
-        for (uint32_t k = b; k < e; ++k) dst_base[w + (k - b)] = src_base[k];
-        w += e - b;
+    uint32_t w = s_len[bi*RB_THREADS + t];
+    uint32_t out[4];
+    if (R < n_own) {
+      const uint4 q = *reinterpret_cast<const uint4 *>(o);
+      const uint32_t in[5] = {q.x, q.y, q.z, q.w, o[4]};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        out[k] = w;
+        if (R + k >= n_own) continue;
+        int j = -1;
+        if (tk[0] == k && tacc[0]) j = 0;
+        if (tk[1] == k && tacc[1]) j = 1;
+        if (j >= 0) {
+          const int n_new = tcnt[j] ? tcnt[j][bi] : 0;
+          for (int x = 0; x < n_new; ++x) dst_base[w + x] = tpj[j][poff[j] + x];
+          poff[j] += n_new;
+          w += n_new;
+        }
+        else {
+          const uint32_t n = in[k + 1] - in[k];
+          for (uint32_t x = 0; x < n; ++x) dst_base[w + x] = src_base[in[k] + x];
+          w += n;
+        }
       }
     }
-    poff += n_new;
+    else out[0] = out[1] = out[2] = out[3] = w;       // R == n_own: the closing offset
+    *reinterpret_cast<uint4 *>(a.off_out + (uint64_t)bi*a.in.off_pitch + R) = make_uint4(out[0], out[1], out[2], out[3]);
   }
 }
 
@@ -256,7 +286,7 @@ csr_rebuild_kernel(const PassArgs a) {
 
 size_t
 mh_pass_smem_bytes(int n_nodes) {
-  return (size_t)(n_nodes - 1)*MH_THREADS*sizeof(uint32_t);
+  return (size_t)(n_nodes - 1)*RB_THREADS*sizeof(uint32_t);
 }
 
 template <int MAXN, int MAXJ>
@@ -282,7 +312,7 @@ void
 launch_csr_rebuild(const PassArgs &a, cudaStream_t st) {
   const size_t smem = mh_pass_smem_bytes(a.tree.n_nodes);
   cudaFuncSetAttribute(csr_rebuild_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  csr_rebuild_kernel<<<a.n_tiles, MH_THREADS, smem, st>>>(a);
+  csr_rebuild_kernel<<<a.n_tiles, RB_THREADS, smem, st>>>(a);
 }
 
 }  // namespace epv
