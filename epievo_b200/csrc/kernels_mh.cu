@@ -181,23 +181,21 @@ csr_rebuild_kernel(const PassArgs a) {
   const uint64_t R = 4*((uint64_t)tile*RB_THREADS + t);
   const int hw = stage_header_words(n_br);
 
-  // the (at most two) rows of the quad whose site has this pass's colour
-  int tk[2] = {-1, -1};
-  const uint16_t *tcnt[2] = {nullptr, nullptr};
-  const double *tpj[2] = {nullptr, nullptr};
-  bool tacc[2] = {false, false};
-  {
-    const int k0 = (int)((a.colour + 3 - (int)((R + own_lo) % 3)) % 3);
-#pragma unroll
-    for (int j = 0; j < 2; ++j) {
-      const int k = k0 + 3*j;
-      if (k < 4 && R + k < n_own) {
-        const uint32_t so = a.stage_off[(R + k + own_lo)/3];
-        tk[j] = k;
-        tacc[j] = so != STG_REJECTED;
-        if (so < STG_EMPTY) { tcnt[j] = reinterpret_cast<const uint16_t *>(a.stage + so); tpj[j] = a.stage + so + hw; }
-      }
-    }
+  // the (at most two) rows of the quad whose site has this pass's colour: row k0 and, when
+  // k0 == 0, row 3.  Kept in scalars (no dynamically indexed local arrays).
+  const int k0 = (int)((a.colour + 3 - (int)((R + own_lo) % 3)) % 3);
+  bool acc0 = false, acc1 = false;
+  const uint16_t *cnt0 = nullptr, *cnt1 = nullptr;
+  const double *pj0 = nullptr, *pj1 = nullptr;
+  if (R + k0 < n_own) {
+    const uint32_t so = a.stage_off[(R + k0 + own_lo)/3];
+    acc0 = so != STG_REJECTED;
+    if (so < STG_EMPTY) { cnt0 = reinterpret_cast<const uint16_t *>(a.stage + so); pj0 = a.stage + so + hw; }
+  }
+  if (k0 == 0 && R + 3 < n_own) {
+    const uint32_t so = a.stage_off[(R + 3 + own_lo)/3];
+    acc1 = so != STG_REJECTED;
+    if (so < STG_EMPTY) { cnt1 = reinterpret_cast<const uint16_t *>(a.stage + so); pj1 = a.stage + so + hw; }
   }
 
   // ---- new row lengths of the quad, summed per thread -------------------------------
@@ -211,8 +209,8 @@ csr_rebuild_kernel(const PassArgs a) {
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         if (R + k >= n_own) len[k] = 0;
-#pragma unroll
-        for (int j = 0; j < 2; ++j) if (tk[j] == k && tacc[j]) len[k] = tcnt[j] ? tcnt[j][bi] : 0u;
+        if (k < 3 && k == k0 && acc0) len[k] = cnt0 ? cnt0[bi] : 0u;
+        if (k == 3 && acc1) len[k] = cnt1 ? cnt1[bi] : 0u;
         sum += len[k];
       }
     }
@@ -247,7 +245,7 @@ csr_rebuild_kernel(const PassArgs a) {
   if (s_fail || R > n_own) return;
 
   // ---- write the rebuilt rows ------------------------------------------------------------
-  int poff[2] = {0, 0};
+  int poff0 = 0, poff1 = 0;
   for (int bi = 0; bi < n_br; ++bi) {
     const uint32_t *o = a.in.off + (uint64_t)bi*a.in.off_pitch + R;
     const double *src_base = a.in.jmp + a.in.jbase[bi];
@@ -261,13 +259,16 @@ csr_rebuild_kernel(const PassArgs a) {
       for (int k = 0; k < 4; ++k) {
         out[k] = w;
         if (R + k >= n_own) continue;
-        int j = -1;
-        if (tk[0] == k && tacc[0]) j = 0;
-        if (tk[1] == k && tacc[1]) j = 1;
-        if (j >= 0) {
-          const int n_new = tcnt[j] ? tcnt[j][bi] : 0;
-          for (int x = 0; x < n_new; ++x) dst_base[w + x] = tpj[j][poff[j] + x];
-          poff[j] += n_new;
+        if (k < 3 && k == k0 && acc0) {
+          const int n_new = cnt0 ? cnt0[bi] : 0;
+          for (int x = 0; x < n_new; ++x) dst_base[w + x] = pj0[poff0 + x];
+          poff0 += n_new;
+          w += n_new;
+        }
+        else if (k == 3 && acc1) {
+          const int n_new = cnt1 ? cnt1[bi] : 0;
+          for (int x = 0; x < n_new; ++x) dst_base[w + x] = pj1[poff1 + x];
+          poff1 += n_new;
           w += n_new;
         }
         else {

@@ -11,12 +11,50 @@ constexpr int SS_THREADS = 256;
 
 // Per-branch J/D over every interior site of the shard
 // (get_sufficient_statistics, ParamEstimation.cpp:92-114, built on
-// add_sufficient_statistics, Path.cpp:267-301).  Rows whose three paths have no jumps
-// (the vast majority) only contribute tot_time to D[triplet]: they are COUNTED per
-// triplet with warp match + one shared-memory integer atomic per distinct triplet;
-// rows with events take the three-way merge and add into shared-memory accumulators.
-// acc layout per branch: [0..8) D partial sums (double), [8..16) J counts, [16..24)
-// event-free row counts (both uint64 bit patterns in the same array).
+// add_sufficient_statistics, Path.cpp:267-301).
+//
+// Mapping: lane = site, a warp walks chunks of 32 x SS_ITERS consecutive sites; for each
+// chunk the BRANCH loop is outside the site loop, so one coalesced 4-byte load per row
+// brings its CSR offset and the neighbours' offsets / state words come from warp
+// shuffles (three extra loads per 32 rows for the chunk edges).  Rows whose three paths
+// have no jump (91-98 %) only add tot_time to D[triplet]: each lane counts them in eight
+// 8-bit fields of one 64-bit register, reduced once per (chunk, branch) with a warp
+// shuffle tree; rows with events take the three-way merge (same strict-'<' tie-breaks as
+// the reference) into shared-memory accumulators.  One global atomic per (branch,
+// triplet) per CTA.  acc layout per branch: [0..8) D partial sums (double), [8..16) J
+// counts, [16..24) event-free row counts (uint64 bit patterns in the same array).
+constexpr int SS_ITERS = 16;
+
+__device__ __forceinline__ uint64_t
+state_word(const uint8_t *state, int W, uint64_t site) {
+  uint64_t x = 0;
+  for (int b = 0; b < W && b < 8; ++b) x |= (uint64_t)state[site*W + b] << (8*b);
+  return x;
+}
+
+__device__ __forceinline__ void
+merge_row(const Row &L, const Row &M, const Row &R, double *s_D, unsigned *s_J, unsigned *s_C) {
+  int trip = L.init*4 + M.init*2 + R.init, i = 0, j = 0, k = 0;
+  double prev = 0.0;
+  const double INF = __longlong_as_double(0x7ff0000000000000LL);
+  for (;;) {
+    if (i >= L.n && j >= M.n && k >= R.n) break;
+    const double tl = i < L.n ? L.ptr[i] : INF;
+    const double tm = j < M.n ? M.ptr[j] : INF;
+    const double tr = k < R.n ? R.ptr[k] : INF;
+    double tn; int flip;
+    if (tl < fmin(tm, tr)) { tn = tl; flip = 4; ++i; }
+    else if (tm < tr) { tn = tm; flip = 2; ++j; atomicAdd(&s_J[trip], 1u); }
+    else { tn = tr; flip = 1; ++k; }
+    atomicAdd(&s_D[trip], tn - prev);
+    prev = tn; trip ^= flip;
+  }
+  // final segment tot_time - prev: tot_time is added in the fold as (rows ending in
+  // this triplet) * tot_time, the -prev part here
+  atomicAdd(&s_D[trip], -prev);
+  atomicAdd(&s_C[trip], 1u);
+}
+
 __global__ void __launch_bounds__(SS_THREADS)
 suffstats_kernel(const PathView pv, const uint8_t *state, int W, int n_br,
                  uint64_t lo, uint64_t hi, unsigned long long *acc) {
@@ -26,45 +64,70 @@ suffstats_kernel(const PathView pv, const uint8_t *state, int W, int n_br,
   unsigned *s_C = s_J + n_br*8;                                   // [n_br*8]
   for (int i = threadIdx.x; i < n_br*8; i += SS_THREADS) { s_D[i] = 0.0; s_J[i] = 0; s_C[i] = 0; }
   __syncthreads();
+  constexpr unsigned FULL = 0xffffffffu;
   const int lane = threadIdx.x & 31;
-  const uint64_t span = hi - lo;
-  const uint64_t n_iter = (span + (uint64_t)gridDim.x*SS_THREADS - 1)/((uint64_t)gridDim.x*SS_THREADS);
-  for (uint64_t it = 0; it < n_iter; ++it) {
-    const uint64_t s = lo + (it*gridDim.x + blockIdx.x)*SS_THREADS + threadIdx.x;
-    const bool live = s < hi;
+  const uint64_t warp_id = ((uint64_t)blockIdx.x*SS_THREADS + threadIdx.x) >> 5;
+  const uint64_t n_warps = ((uint64_t)gridDim.x*SS_THREADS) >> 5;
+  const uint64_t chunk = 32*SS_ITERS;
+  const uint64_t n_chunks = (hi - lo + chunk - 1)/chunk;
+  const bool wide = W > 8;                       // > 64 nodes: state bits read per row
+  for (uint64_t ch = warp_id; ch < n_chunks; ch += n_warps) {
+    const uint64_t c0 = lo + ch*chunk;
     for (int bi = 0; bi < n_br; ++bi) {
-      int key = 8;
-      Row L, M, R;
-      if (live) {
-        L = load_row(pv, state, W, bi, s - 1);
-        M = load_row(pv, state, W, bi, s);
-        R = load_row(pv, state, W, bi, s + 1);
-        if ((L.n | M.n | R.n) == 0) key = L.init*4 + M.init*2 + R.init;
-      }
-      const unsigned peers = __match_any_sync(0xffffffffu, key);
-      if (key < 8) {
-        if (lane == __ffs(peers) - 1) atomicAdd(&s_C[bi*8 + key], (unsigned)__popc(peers));
-      }
-      else if (live) {
-        int trip = L.init*4 + M.init*2 + R.init, i = 0, j = 0, k = 0;
-        double prev = 0.0;
-        const double INF = __longlong_as_double(0x7ff0000000000000LL);
-        for (;;) {
-          if (i >= L.n && j >= M.n && k >= R.n) break;
-          const double tl = i < L.n ? L.ptr[i] : INF;
-          const double tm = j < M.n ? M.ptr[j] : INF;
-          const double tr = k < R.n ? R.ptr[k] : INF;
-          double tn; int flip;
-          if (tl < fmin(tm, tr)) { tn = tl; flip = 4; ++i; }
-          else if (tm < tr) { tn = tm; flip = 2; ++j; atomicAdd(&s_J[bi*8 + trip], 1u); }
-          else { tn = tr; flip = 1; ++k; }
-          atomicAdd(&s_D[bi*8 + trip], tn - prev);
-          prev = tn; trip ^= flip;
+      const uint32_t *o = pv.off + (uint64_t)bi*pv.off_pitch;
+      const double *jb = pv.jmp + pv.jbase[bi];
+      uint64_t packed = 0;                       // eight 8-bit counters of event-free rows
+      for (int it = 0; it < SS_ITERS; ++it) {
+        const uint64_t w0 = c0 + 32*it;          // first site of this warp row
+        if (w0 >= hi) break;
+        const uint64_t s = w0 + lane;
+        const bool live = s < hi;
+        // fast addressing needs sites w0-1 .. w0+33 inside the CSR
+        const bool fast = w0 - 1 >= pv.own_lo && w0 + 34 <= pv.own_hi && !wide;
+        Row L, M, R;
+        if (fast) {
+          const uint64_t r = s - pv.own_lo;
+          const uint32_t om = o[r];
+          // lanes 0..2 fetch the three offsets the shuffles cannot supply
+          const uint32_t ex = lane < 3 ? o[(w0 - pv.own_lo) + (lane == 0 ? -1 : 31 + lane)] : 0u;
+          uint32_t om1 = __shfl_up_sync(FULL, om, 1), op1 = __shfl_down_sync(FULL, om, 1),
+            op2 = __shfl_down_sync(FULL, om, 2);
+          const uint32_t e0 = __shfl_sync(FULL, ex, 0), e1 = __shfl_sync(FULL, ex, 1),
+            e2 = __shfl_sync(FULL, ex, 2);
+          if (lane == 0) om1 = e0;
+          if (lane == 31) { op1 = e1; op2 = e2; }
+          if (lane == 30) op2 = e1;
+          const uint64_t wm = state_word(state, W, s);
+          uint64_t wl = __shfl_up_sync(FULL, wm, 1), wr = __shfl_down_sync(FULL, wm, 1);
+          if (lane == 0) wl = state_word(state, W, s - 1);
+          if (lane == 31) wr = state_word(state, W, s + 1);
+          L.n = (int)(om - om1); M.n = (int)(op1 - om); R.n = (int)(op2 - op1);
+          L.ptr = jb + om1; M.ptr = jb + om; R.ptr = jb + op1;
+          L.init = (int)((wl >> (bi + 1)) & 1); M.init = (int)((wm >> (bi + 1)) & 1);
+          R.init = (int)((wr >> (bi + 1)) & 1);
         }
-        // final segment: tot_time - prev; tot_time is added on the host side of the
-        // fold as (count of rows ending in this triplet) -- keep it exact here instead
-        atomicAdd(&s_D[bi*8 + trip], -prev);
-        atomicAdd(&s_C[bi*8 + trip], 1u);
+        else if (live) {
+          L = load_row(pv, state, W, bi, s - 1);
+          M = load_row(pv, state, W, bi, s);
+          R = load_row(pv, state, W, bi, s + 1);
+        }
+        if (live) {
+          if ((L.n | M.n | R.n) == 0) packed += 1ull << (8*(L.init*4 + M.init*2 + R.init));
+          else merge_row(L, M, R, s_D + bi*8, s_J + bi*8, s_C + bi*8);
+        }
+      }
+      // reduce the packed counters over the warp: fields stay below 2^8 per lane (<= 16),
+      // so split into two words of four 16-bit fields before summing 32 lanes
+      uint64_t ev = packed & 0x00ff00ff00ff00ffull, od = (packed >> 8) & 0x00ff00ff00ff00ffull;
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) {
+        ev += __shfl_xor_sync(FULL, ev, d);
+        od += __shfl_xor_sync(FULL, od, d);
+      }
+      if (lane < 8) {
+        const uint64_t src = (lane & 1) ? od : ev;
+        const unsigned c = (unsigned)((src >> (16*(lane >> 1))) & 0xffffu);
+        if (c) atomicAdd(&s_C[bi*8 + lane], c);
       }
     }
   }
@@ -208,7 +271,8 @@ launch_suffstats(const PathView &pv, const uint8_t *state, int W, const TreeDev 
   const int n_br = tree.n_nodes - 1;
   cudaMemsetAsync(scratch, 0, (size_t)n_br*24*8, st);
   if (hi > lo) {
-    const uint64_t want = (hi - lo + SS_THREADS - 1)/SS_THREADS;
+    const uint64_t n_chunks = (hi - lo + 32*SS_ITERS - 1)/(32*SS_ITERS);
+    const uint64_t want = (n_chunks + SS_THREADS/32 - 1)/(SS_THREADS/32);
     const unsigned blocks = (unsigned)(want < (uint64_t)sm_count*8 ? want : (uint64_t)sm_count*8);
     const size_t smem = (size_t)n_br*8*(8 + 4 + 4);
     cudaFuncSetAttribute(suffstats_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

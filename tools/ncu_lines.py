@@ -7,10 +7,11 @@ import sys
 
 rep = sys.argv[1]
 top = int(sys.argv[2]) if len(sys.argv) > 2 else 40
+filt = sys.argv[3] if len(sys.argv) > 3 else ""          # substring of the kernel name
 out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass"],
                      capture_output=True, text=True).stdout
 rows = csv.reader(out.splitlines())
-fname, hdr, agg, kernels = None, None, {}, 0
+fname, hdr, agg, kernels, func = None, None, {}, 0, ""
 for r in rows:
     if not r:
         continue
@@ -18,6 +19,7 @@ for r in rows:
         fname = r[1].split("/")[-1]
         continue
     if r[0] == "Function Name":
+        func = r[1]
         continue
     if r[0] == "Line No":
         hdr = r
@@ -25,7 +27,7 @@ for r in rows:
         i_thr = hdr.index("Thread Instructions Executed")
         i_smp = hdr.index("# Samples")
         continue
-    if hdr and r[0] not in ("", "-"):          # a source-line summary row
+    if hdr and r[0] not in ("", "-") and filt in func:          # a source-line summary row
         try:
             key = (fname, int(r[0]), r[1].strip()[:90])
             a = agg.setdefault(key, [0, 0, 0])
