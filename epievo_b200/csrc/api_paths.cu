@@ -141,7 +141,8 @@ int epv_upload_paths(epv_ctx *c, uint64_t n_sites, uint64_t n_nodes, const uint8
     std::vector<uint64_t> cap(n_br);
     for (int bi = 0; bi < n_br; ++bi) cap[bi] = capacity_for(count[bi], n_own);
     c->n_sites = n_sites;
-    c->W = (c->n_nodes + 7)/8;
+    c->W = 1;                                         // bytes of state bits per site, a power of two
+    while (c->W*8 < c->n_nodes) c->W *= 2;            // so that <= 64 nodes are one aligned load
     c->off_pitch = (n_own + 1 + 4 + 31) & ~31ull;     // room for the rebuild kernel's 16-byte vectors
     c->n_tiles = (uint32_t)((n_own + 1 + RB_TILE_ROWS - 1)/RB_TILE_ROWS);
     if (int r = alloc_jumps(c, cap, c->d_jmp, c->h_jbase, c->jmp_total_cap)) return r;

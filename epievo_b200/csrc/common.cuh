@@ -127,6 +127,18 @@ state_bit(const uint8_t *state, int W, uint64_t site, int node) {
   return (state[site*W + (node >> 3)] >> (node & 7)) & 1;
 }
 
+// All state bits of one site as 64-bit words (W is a power of two; W <= 8: one load).
+__device__ __forceinline__ uint64_t
+state_word(const uint8_t *state, int W, uint64_t site, int word = 0) {
+  const uint8_t *p = state + site*W;
+  switch (W) {
+  case 1: return *p;
+  case 2: return *reinterpret_cast<const uint16_t *>(p);
+  case 4: return *reinterpret_cast<const uint32_t *>(p);
+  default: return reinterpret_cast<const uint64_t *>(p)[word];
+  }
+}
+
 template <typename T>
 __device__ __forceinline__ T
 warp_sum(T v) {

@@ -23,7 +23,9 @@ __host__ __device__ inline RecLayout
 layout_of(int n_nodes) {
   RecLayout L;
   L.n_br = n_nodes - 1;
-  L.sw = ((n_nodes + 7)/8 + 7)/8;
+  int W = 1;
+  while (W*8 < n_nodes) W *= 2;                 // the context's padded state width
+  L.sw = (W + 7)/8;
   L.cw = (L.n_br + 3)/4;
   return L;
 }

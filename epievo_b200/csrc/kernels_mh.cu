@@ -46,7 +46,8 @@ mh_update_kernel(const PassArgs a) {
   const uint64_t st = 3*g + a.colour;                          // the group's target site
   const int64_t gsite = a.global0 + (int64_t)st;
 
-  constexpr int PB = 16, QCAP = 8;
+  // interval stack / jump queue capacities grow with the tree (expected use ~ 0.1 / 0.07 per branch)
+  constexpr int PB = MAXN <= 16 ? 16 : MAXN/2, QCAP = MAXN <= 16 ? 8 : MAXN/4;
   FlatScratch<MAXN, PB, QCAP> S;
   double pj_local[MAXJ];
   uint16_t pn[MAXN];

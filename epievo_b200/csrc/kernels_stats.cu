@@ -23,14 +23,8 @@ constexpr int SS_THREADS = 256;
 // the reference) into shared-memory accumulators.  One global atomic per (branch,
 // triplet) per CTA.  acc layout per branch: [0..8) D partial sums (double), [8..16) J
 // counts, [16..24) event-free row counts (uint64 bit patterns in the same array).
-constexpr int SS_ITERS = 16;
-
-__device__ __forceinline__ uint64_t
-state_word(const uint8_t *state, int W, uint64_t site) {
-  uint64_t x = 0;
-  for (int b = 0; b < W && b < 8; ++b) x |= (uint64_t)state[site*W + b] << (8*b);
-  return x;
-}
+constexpr int SS_ITERS = 16;     // warp rows (of 32 sites) per chunk
+constexpr int SS_GROUP = 8;      // branches whose packed counters live in registers at once
 
 __device__ __forceinline__ void
 merge_row(const Row &L, const Row &M, const Row &R, double *s_D, unsigned *s_J, unsigned *s_C) {
@@ -70,64 +64,59 @@ suffstats_kernel(const PathView pv, const uint8_t *state, int W, int n_br,
   const uint64_t n_warps = ((uint64_t)gridDim.x*SS_THREADS) >> 5;
   const uint64_t chunk = 32*SS_ITERS;
   const uint64_t n_chunks = (hi - lo + chunk - 1)/chunk;
-  const bool wide = W > 8;                       // > 64 nodes: state bits read per row
   for (uint64_t ch = warp_id; ch < n_chunks; ch += n_warps) {
     const uint64_t c0 = lo + ch*chunk;
-    for (int bi = 0; bi < n_br; ++bi) {
-      const uint32_t *o = pv.off + (uint64_t)bi*pv.off_pitch;
-      const double *jb = pv.jmp + pv.jbase[bi];
-      uint64_t packed = 0;                       // eight 8-bit counters of event-free rows
+    for (int b0 = 0; b0 < n_br; b0 += SS_GROUP) {
+      uint64_t packed[SS_GROUP];                 // per branch: eight 8-bit counters of event-free rows
+#pragma unroll
+      for (int g = 0; g < SS_GROUP; ++g) packed[g] = 0;
       for (int it = 0; it < SS_ITERS; ++it) {
-        const uint64_t w0 = c0 + 32*it;          // first site of this warp row
-        if (w0 >= hi) break;
-        const uint64_t s = w0 + lane;
-        const bool live = s < hi;
-        // fast addressing needs sites w0-1 .. w0+33 inside the CSR
-        const bool fast = w0 - 1 >= pv.own_lo && w0 + 34 <= pv.own_hi && !wide;
-        Row L, M, R;
-        if (fast) {
-          const uint64_t r = s - pv.own_lo;
-          const uint32_t om = o[r];
-          // lanes 0..2 fetch the three offsets the shuffles cannot supply
-          const uint32_t ex = lane < 3 ? o[(w0 - pv.own_lo) + (lane == 0 ? -1 : 31 + lane)] : 0u;
-          uint32_t om1 = __shfl_up_sync(FULL, om, 1), op1 = __shfl_down_sync(FULL, om, 1),
-            op2 = __shfl_down_sync(FULL, om, 2);
-          const uint32_t e0 = __shfl_sync(FULL, ex, 0), e1 = __shfl_sync(FULL, ex, 1),
-            e2 = __shfl_sync(FULL, ex, 2);
-          if (lane == 0) om1 = e0;
-          if (lane == 31) { op1 = e1; op2 = e2; }
-          if (lane == 30) op2 = e1;
-          const uint64_t wm = state_word(state, W, s);
-          uint64_t wl = __shfl_up_sync(FULL, wm, 1), wr = __shfl_down_sync(FULL, wm, 1);
-          if (lane == 0) wl = state_word(state, W, s - 1);
-          if (lane == 31) wr = state_word(state, W, s + 1);
-          L.n = (int)(om - om1); M.n = (int)(op1 - om); R.n = (int)(op2 - op1);
-          L.ptr = jb + om1; M.ptr = jb + om; R.ptr = jb + op1;
-          L.init = (int)((wl >> (bi + 1)) & 1); M.init = (int)((wm >> (bi + 1)) & 1);
-          R.init = (int)((wr >> (bi + 1)) & 1);
-        }
-        else if (live) {
-          L = load_row(pv, state, W, bi, s - 1);
-          M = load_row(pv, state, W, bi, s);
-          R = load_row(pv, state, W, bi, s + 1);
-        }
-        if (live) {
-          if ((L.n | M.n | R.n) == 0) packed += 1ull << (8*(L.init*4 + M.init*2 + R.init));
+        const uint64_t s = c0 + 32*it + lane;
+        if (s >= hi) break;
+        // whole neighbourhood in the CSR and <= 64 nodes: direct offsets + one state word per site
+        const bool fast = s - 1 >= pv.own_lo && s + 1 < pv.own_hi && W <= 8;
+        uint64_t wl = 0, wm = 0, wr = 0;
+        if (fast) { wl = state_word(state, W, s - 1); wm = state_word(state, W, s); wr = state_word(state, W, s + 1); }
+#pragma unroll
+        for (int g = 0; g < SS_GROUP; ++g) {
+          const int bi = b0 + g;
+          if (bi >= n_br) break;
+          Row L, M, R;
+          if (fast) {
+            const uint32_t *o = pv.off + (uint64_t)bi*pv.off_pitch + (s - 1 - pv.own_lo);
+            const uint32_t o0 = o[0], o1 = o[1], o2 = o[2], o3 = o[3];
+            const double *jb = pv.jmp + pv.jbase[bi];
+            L.n = (int)(o1 - o0); M.n = (int)(o2 - o1); R.n = (int)(o3 - o2);
+            L.ptr = jb + o0; M.ptr = jb + o1; R.ptr = jb + o2;
+            L.init = (int)((wl >> (bi + 1)) & 1); M.init = (int)((wm >> (bi + 1)) & 1);
+            R.init = (int)((wr >> (bi + 1)) & 1);
+          }
+          else {
+            L = load_row(pv, state, W, bi, s - 1);
+            M = load_row(pv, state, W, bi, s);
+            R = load_row(pv, state, W, bi, s + 1);
+          }
+          if ((L.n | M.n | R.n) == 0) packed[g] += 1ull << (8*(L.init*4 + M.init*2 + R.init));
           else merge_row(L, M, R, s_D + bi*8, s_J + bi*8, s_C + bi*8);
         }
       }
-      // reduce the packed counters over the warp: fields stay below 2^8 per lane (<= 16),
-      // so split into two words of four 16-bit fields before summing 32 lanes
-      uint64_t ev = packed & 0x00ff00ff00ff00ffull, od = (packed >> 8) & 0x00ff00ff00ff00ffull;
+      // reduce the packed counters over the warp: a field is <= 16 per lane, so two words
+      // of four 16-bit fields hold the sums over 32 lanes
 #pragma unroll
-      for (int d = 16; d > 0; d >>= 1) {
-        ev += __shfl_xor_sync(FULL, ev, d);
-        od += __shfl_xor_sync(FULL, od, d);
-      }
-      if (lane < 8) {
-        const uint64_t src = (lane & 1) ? od : ev;
-        const unsigned c = (unsigned)((src >> (16*(lane >> 1))) & 0xffffu);
-        if (c) atomicAdd(&s_C[bi*8 + lane], c);
+      for (int g = 0; g < SS_GROUP; ++g) {
+        const int bi = b0 + g;
+        if (bi >= n_br) break;
+        uint64_t ev = packed[g] & 0x00ff00ff00ff00ffull, od = (packed[g] >> 8) & 0x00ff00ff00ff00ffull;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+          ev += __shfl_xor_sync(FULL, ev, d);
+          od += __shfl_xor_sync(FULL, od, d);
+        }
+        if (lane < 8) {
+          const uint64_t src = (lane & 1) ? od : ev;
+          const unsigned c = (unsigned)((src >> (16*(lane >> 1))) & 0xffffu);
+          if (c) atomicAdd(&s_C[bi*8 + lane], c);
+        }
       }
     }
   }

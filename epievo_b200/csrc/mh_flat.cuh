@@ -48,8 +48,9 @@ struct StateWin {
       for (int j = 0; j < WORDS; ++j) w[k][j] = 0;
       const int64_t site = (int64_t)s + k - 2;
       if (site >= 0 && site < (int64_t)n_sites)
-        for (int b = 0; b < W; ++b)
-          w[k][WORDS == 1 ? 0 : b >> 3] |= (uint64_t)state[(uint64_t)site*W + b] << (8*(b & 7));
+#pragma unroll
+        for (int j = 0; j < WORDS; ++j)
+          if (j*8 < W) w[k][j] = state_word(state, W, (uint64_t)site, j);
     }
   }
   // d = site offset relative to s (-2..2)
