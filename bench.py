@@ -327,6 +327,20 @@ def main():
                 "rebuild_kernel_avg_ms": rebuild_ms / max(1, mh_launches),
                 "rebuild_kernel_share_of_step": rebuild_ms / ms if ms > 0 else None}
 
+    # ---- the J/D pass on its own (epv_suffstats: kernel + 1 KB read-back), HBM roofline ----
+    sst0, sst1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ctx.suffstats()
+    sst0.record(stream)
+    for _ in range(5):
+        ctx.suffstats()
+    sst1.record(stream)
+    torch.cuda.synchronize()
+    ss_ms = sst0.elapsed_time(sst1) / 5
+    ss_bytes = n_own * n_br * row_bytes
+    suffstats = {"ms": ss_ms, "algorithmic_bytes": ss_bytes, "achieved_gbs": ss_bytes / (ss_ms * 1e-3) / 1e9,
+                 "frac_of_hbm_peak": ss_bytes / (ss_ms * 1e-3) / 1e9 / peak,
+                 "rows_per_s": n_own * n_br / (ss_ms * 1e-3)}
+
     # ---- CPU baseline (rank 0, N=1 only) ---------------------------------------------------
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -345,7 +359,7 @@ def main():
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": workload_config(args, n_br), "clocks": clk, "e2e": e2e,
             "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu_baseline,
-            "acc_rate": acc,
+            "acc_rate": acc, "suffstats_pass": suffstats,
         }
         print(json.dumps(line))
     ctx.close()

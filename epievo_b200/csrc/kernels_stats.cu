@@ -13,50 +13,86 @@ constexpr int SS_THREADS = 256;
 // (get_sufficient_statistics, ParamEstimation.cpp:92-114, built on
 // add_sufficient_statistics, Path.cpp:267-301).
 //
-// Mapping: lane = site, a warp walks chunks of 32 x SS_ITERS consecutive sites; for each
-// chunk the BRANCH loop is outside the site loop, so one coalesced 4-byte load per row
-// brings its CSR offset and the neighbours' offsets / state words come from warp
-// shuffles (three extra loads per 32 rows for the chunk edges).  Rows whose three paths
-// have no jump (91-98 %) only add tot_time to D[triplet]: each lane counts them in eight
-// 8-bit fields of one 64-bit register, reduced once per (chunk, branch) with a warp
-// shuffle tree; rows with events take the three-way merge (same strict-'<' tie-breaks as
-// the reference) into shared-memory accumulators.  One global atomic per (branch,
-// triplet) per CTA.  acc layout per branch: [0..8) D partial sums (double), [8..16) J
-// counts, [16..24) event-free row counts (uint64 bit patterns in the same array).
+// lane = site; a warp walks chunks of 32 x SS_ITERS consecutive sites, SS_GROUP branches
+// at a time.  Two kinds of rows:
+//  * event-free rows (the three paths have no jump on the branch; 85-98 %) only add
+//    tot_time to D[triplet]: each lane counts them in eight 8-bit fields of one 64-bit
+//    register per branch, reduced once per (chunk, branch) with a warp shuffle tree;
+//  * rows with events are NOT merged inline (that would run the three-way merge with a
+//    few lanes active on almost every iteration): the lane appends (site, branch) to a
+//    per-warp shared-memory queue (ballot + popc), and the warp merges queued rows 32 at
+//    a time, every lane one row (same strict-'<' tie-breaks as the reference).  Their D
+//    terms are accumulated in shared memory as 64-bit fixed point (quantum
+//    tot_time * 2^-40: native integer atomics instead of fp64 CAS loops; the rounding is
+//    <= 2^-41 of a branch length per term, far inside the 1e-9 parity bound), J as
+//    integers.
+// One global atomic per (branch, triplet) per CTA.  acc layout per branch: [0..8) D
+// partial sums (double), [8..16) J counts, [16..24) event-free row counts.
 constexpr int SS_ITERS = 16;     // warp rows (of 32 sites) per chunk
 constexpr int SS_GROUP = 8;      // branches whose packed counters live in registers at once
+constexpr int SS_QCAP = 96;      // queue entries per warp (drained in batches of 32)
+constexpr double SS_FIX = 1099511627776.0;   // 2^40
+
+struct StatsAcc {
+  long long *Dfix;     // [n_br*8] fixed-point D of rows with events
+  unsigned *J;         // [n_br*8]
+  unsigned *C;         // [n_br*8] event-free rows
+};
 
 __device__ __forceinline__ void
-merge_row(const Row &L, const Row &M, const Row &R, double *s_D, unsigned *s_J, unsigned *s_C) {
+load3(const PathView &pv, const uint8_t *state, int W, int bi, uint64_t s, Row &L, Row &M, Row &R) {
+  if (s - 1 >= pv.own_lo && s + 1 < pv.own_hi && W <= 8) {
+    const uint32_t *o = pv.off + (uint64_t)bi*pv.off_pitch + (s - 1 - pv.own_lo);
+    const uint32_t o0 = o[0], o1 = o[1], o2 = o[2], o3 = o[3];
+    const double *jb = pv.jmp + pv.jbase[bi];
+    L.n = (int)(o1 - o0); M.n = (int)(o2 - o1); R.n = (int)(o3 - o2);
+    L.ptr = jb + o0; M.ptr = jb + o1; R.ptr = jb + o2;
+    L.init = (int)((state_word(state, W, s - 1) >> (bi + 1)) & 1);
+    M.init = (int)((state_word(state, W, s) >> (bi + 1)) & 1);
+    R.init = (int)((state_word(state, W, s + 1) >> (bi + 1)) & 1);
+  }
+  else {
+    L = load_row(pv, state, W, bi, s - 1);
+    M = load_row(pv, state, W, bi, s);
+    R = load_row(pv, state, W, bi, s + 1);
+  }
+}
+
+// Three-way merge of one row triple (add_sufficient_statistics, Path.cpp:267-301).
+__device__ __forceinline__ void
+merge_row(const Row &L, const Row &M, const Row &R, double tot, const StatsAcc &A, int bi) {
   int trip = L.init*4 + M.init*2 + R.init, i = 0, j = 0, k = 0;
   double prev = 0.0;
+  const double scale = SS_FIX/tot;
   const double INF = __longlong_as_double(0x7ff0000000000000LL);
   for (;;) {
-    if (i >= L.n && j >= M.n && k >= R.n) break;
     const double tl = i < L.n ? L.ptr[i] : INF;
     const double tm = j < M.n ? M.ptr[j] : INF;
     const double tr = k < R.n ? R.ptr[k] : INF;
     double tn; int flip;
     if (tl < fmin(tm, tr)) { tn = tl; flip = 4; ++i; }
-    else if (tm < tr) { tn = tm; flip = 2; ++j; atomicAdd(&s_J[trip], 1u); }
+    else if (tm < tr) { tn = tm; flip = 2; ++j; }
     else { tn = tr; flip = 1; ++k; }
-    atomicAdd(&s_D[trip], tn - prev);
+    const bool end = !(tn < INF);
+    if (end) tn = tot;
+    atomicAdd(reinterpret_cast<unsigned long long *>(&A.Dfix[bi*8 + trip]),
+              (unsigned long long)__double2ll_rn((tn - prev)*scale));
+    if (end) break;
+    if (flip == 2) atomicAdd(&A.J[bi*8 + trip], 1u);
     prev = tn; trip ^= flip;
   }
-  // final segment tot_time - prev: tot_time is added in the fold as (rows ending in
-  // this triplet) * tot_time, the -prev part here
-  atomicAdd(&s_D[trip], -prev);
-  atomicAdd(&s_C[trip], 1u);
 }
 
-__global__ void __launch_bounds__(SS_THREADS)
-suffstats_kernel(const PathView pv, const uint8_t *state, int W, int n_br,
+__global__ void __launch_bounds__(SS_THREADS, 3)
+suffstats_kernel(const PathView pv, const uint8_t *state, int W, int n_br, const double *branch,
                  uint64_t lo, uint64_t hi, unsigned long long *acc) {
   extern __shared__ unsigned long long s_raw[];
-  double *s_D = reinterpret_cast<double *>(s_raw);               // [n_br*8]
-  unsigned *s_J = reinterpret_cast<unsigned *>(s_raw + n_br*8);   // [n_br*8]
-  unsigned *s_C = s_J + n_br*8;                                   // [n_br*8]
-  for (int i = threadIdx.x; i < n_br*8; i += SS_THREADS) { s_D[i] = 0.0; s_J[i] = 0; s_C[i] = 0; }
+  StatsAcc A;
+  A.Dfix = reinterpret_cast<long long *>(s_raw);                  // [n_br*8]
+  A.J = reinterpret_cast<unsigned *>(s_raw + n_br*8);             // [n_br*8]
+  A.C = A.J + n_br*8;                                             // [n_br*8]
+  unsigned *s_queue = A.C + n_br*8 + (threadIdx.x >> 5)*SS_QCAP;  // this warp's queue
+  for (int i = threadIdx.x; i < n_br*8; i += SS_THREADS) { A.Dfix[i] = 0; A.J[i] = 0; A.C[i] = 0; }
   __syncthreads();
   constexpr unsigned FULL = 0xffffffffu;
   const int lane = threadIdx.x & 31;
@@ -66,38 +102,61 @@ suffstats_kernel(const PathView pv, const uint8_t *state, int W, int n_br,
   const uint64_t n_chunks = (hi - lo + chunk - 1)/chunk;
   for (uint64_t ch = warp_id; ch < n_chunks; ch += n_warps) {
     const uint64_t c0 = lo + ch*chunk;
+    int qn = 0;                                  // queue fill (warp-uniform)
+    // merge 32 queued rows (or the last qn), one per lane
+    auto drain = [&](int n_take) {
+      __syncwarp();
+      if (lane < n_take) {
+        const unsigned it = s_queue[qn - n_take + lane];
+        const int bi = (int)(it >> 16);
+        const uint64_t s = c0 + (it & 0xffffu);
+        Row L, M, R;
+        load3(pv, state, W, bi, s, L, M, R);
+        merge_row(L, M, R, branch[bi + 1], A, bi);
+      }
+      qn -= n_take;
+      __syncwarp();
+    };
     for (int b0 = 0; b0 < n_br; b0 += SS_GROUP) {
       uint64_t packed[SS_GROUP];                 // per branch: eight 8-bit counters of event-free rows
 #pragma unroll
       for (int g = 0; g < SS_GROUP; ++g) packed[g] = 0;
       for (int it = 0; it < SS_ITERS; ++it) {
+        if (c0 + 32*it >= hi) break;             // warp-uniform
         const uint64_t s = c0 + 32*it + lane;
-        if (s >= hi) break;
-        // whole neighbourhood in the CSR and <= 64 nodes: direct offsets + one state word per site
-        const bool fast = s - 1 >= pv.own_lo && s + 1 < pv.own_hi && W <= 8;
+        const bool live = s < hi;
+        const bool fast = live && s - 1 >= pv.own_lo && s + 1 < pv.own_hi && W <= 8;
         uint64_t wl = 0, wm = 0, wr = 0;
         if (fast) { wl = state_word(state, W, s - 1); wm = state_word(state, W, s); wr = state_word(state, W, s + 1); }
+        // issue the offset loads of the whole branch group first (memory-level parallelism:
+        // the pass is latency-bound, not bandwidth-bound), then classify
+        uint32_t o0[SS_GROUP], o3[SS_GROUP];
+#pragma unroll
+        for (int g = 0; g < SS_GROUP; ++g) {
+          o0[g] = 0; o3[g] = 1;
+          if (fast && b0 + g < n_br) {
+            const uint32_t *o = pv.off + (uint64_t)(b0 + g)*pv.off_pitch + (s - 1 - pv.own_lo);
+            o0[g] = o[0]; o3[g] = o[3];
+          }
+        }
 #pragma unroll
         for (int g = 0; g < SS_GROUP; ++g) {
           const int bi = b0 + g;
           if (bi >= n_br) break;
-          Row L, M, R;
+          bool slow = false;
           if (fast) {
-            const uint32_t *o = pv.off + (uint64_t)bi*pv.off_pitch + (s - 1 - pv.own_lo);
-            const uint32_t o0 = o[0], o1 = o[1], o2 = o[2], o3 = o[3];
-            const double *jb = pv.jmp + pv.jbase[bi];
-            L.n = (int)(o1 - o0); M.n = (int)(o2 - o1); R.n = (int)(o3 - o2);
-            L.ptr = jb + o0; M.ptr = jb + o1; R.ptr = jb + o2;
-            L.init = (int)((wl >> (bi + 1)) & 1); M.init = (int)((wm >> (bi + 1)) & 1);
-            R.init = (int)((wr >> (bi + 1)) & 1);
+            if (o0[g] == o3[g])
+              packed[g] += 1ull << (8*((int)((wl >> (bi + 1)) & 1)*4 + (int)((wm >> (bi + 1)) & 1)*2 +
+                                       (int)((wr >> (bi + 1)) & 1)));
+            else slow = true;
           }
-          else {
-            L = load_row(pv, state, W, bi, s - 1);
-            M = load_row(pv, state, W, bi, s);
-            R = load_row(pv, state, W, bi, s + 1);
+          else slow = live;                      // halo neighbourhood / wide tree: generic loads
+          const unsigned m = __ballot_sync(FULL, slow);
+          if (m) {
+            if (slow) s_queue[qn + __popc(m & ((1u << lane) - 1u))] = ((unsigned)bi << 16) | (unsigned)(32*it + lane);
+            qn += __popc(m);
+            if (qn > SS_QCAP - 32) drain(32);
           }
-          if ((L.n | M.n | R.n) == 0) packed[g] += 1ull << (8*(L.init*4 + M.init*2 + R.init));
-          else merge_row(L, M, R, s_D + bi*8, s_J + bi*8, s_C + bi*8);
         }
       }
       // reduce the packed counters over the warp: a field is <= 16 per lane, so two words
@@ -115,17 +174,19 @@ suffstats_kernel(const PathView pv, const uint8_t *state, int W, int n_br,
         if (lane < 8) {
           const uint64_t src = (lane & 1) ? od : ev;
           const unsigned c = (unsigned)((src >> (16*(lane >> 1))) & 0xffffu);
-          if (c) atomicAdd(&s_C[bi*8 + lane], c);
+          if (c) atomicAdd(&A.C[bi*8 + lane], c);
         }
       }
     }
+    while (qn > 0) drain(qn < 32 ? qn : 32);
   }
   __syncthreads();
   for (int i = threadIdx.x; i < n_br*8; i += SS_THREADS) {
     const int bi = i >> 3, t = i & 7;
-    if (s_D[i] != 0.0) atomicAdd(reinterpret_cast<double *>(acc) + bi*24 + t, s_D[i]);
-    if (s_J[i]) atomicAdd(acc + bi*24 + 8 + t, (unsigned long long)s_J[i]);
-    if (s_C[i]) atomicAdd(acc + bi*24 + 16 + t, (unsigned long long)s_C[i]);
+    if (A.Dfix[i]) atomicAdd(reinterpret_cast<double *>(acc) + bi*24 + t,
+                             (double)A.Dfix[i]*(branch[bi + 1]/SS_FIX));
+    if (A.J[i]) atomicAdd(acc + bi*24 + 8 + t, (unsigned long long)A.J[i]);
+    if (A.C[i]) atomicAdd(acc + bi*24 + 16 + t, (unsigned long long)A.C[i]);
   }
 }
 
@@ -263,9 +324,9 @@ launch_suffstats(const PathView &pv, const uint8_t *state, int W, const TreeDev 
     const uint64_t n_chunks = (hi - lo + 32*SS_ITERS - 1)/(32*SS_ITERS);
     const uint64_t want = (n_chunks + SS_THREADS/32 - 1)/(SS_THREADS/32);
     const unsigned blocks = (unsigned)(want < (uint64_t)sm_count*8 ? want : (uint64_t)sm_count*8);
-    const size_t smem = (size_t)n_br*8*(8 + 4 + 4);
+    const size_t smem = (size_t)n_br*8*(8 + 4 + 4) + (SS_THREADS/32)*SS_QCAP*sizeof(unsigned);
     cudaFuncSetAttribute(suffstats_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    suffstats_kernel<<<blocks, SS_THREADS, smem, st>>>(pv, state, W, n_br, lo, hi, scratch);
+    suffstats_kernel<<<blocks, SS_THREADS, smem, st>>>(pv, state, W, n_br, tree.branch, lo, hi, scratch);
   }
   suffstats_fold_kernel<<<(tree.n_nodes*8 + 127)/128, 128, 0, st>>>(scratch, tree.branch,
                                                                    tree.n_nodes, J, D);
