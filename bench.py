@@ -319,8 +319,14 @@ def main():
     bytes_per_launch = (4.0 / 3.0) * n_own * n_br * row_bytes
     avg_launch_ms = mh_ms / max(1, mh_launches)
     achieved = bytes_per_launch / (avg_launch_ms * 1e-3) / 1e9 if avg_launch_ms > 0 else 0.0
+    traffic = None                      # dram bytes of the kernel from the committed ncu capture
+    tfile = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    if os.path.exists(tfile):
+        tj = json.load(open(tfile))
+        if tj.get("workload") == args.workload and tj.get("n_sites_per_gpu") == args.sites:
+            traffic = tj["traffic_bytes_per_launch"]
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None, "kernel": "mh_update_kernel",
+                "frac": achieved / peak, "traffic": traffic, "kernel": "mh_update_kernel",
                 "peak_source": peak_src, "avg_launch_ms": avg_launch_ms, "launches_timed": mh_launches,
                 "algorithmic_bytes_per_launch": bytes_per_launch, "jumps_per_row": jbar,
                 "kernel_share_of_step": mh_ms / ms if ms > 0 else None,

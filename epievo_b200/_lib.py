@@ -38,6 +38,8 @@ SIGNATURES = {
     "epv_suffstats": (C.c_int, [ctx_p, dp, dp]),
     "epv_llh_grad": (C.c_int, [ctx_p, dp, dp, dp]),
     "epv_scale_jump_times": (C.c_int, [ctx_p, dp]),
+    "epv_mcem_iteration": (C.c_int, [ctx_p, u64, u64, u64, u64, C.c_int, C.c_double, dp, dp, dp, dp,
+                                     dp, dp]),
     "epv_pass": (C.c_int, [ctx_p, C.c_int, u64, u64]),
     "epv_accept_count": (C.c_int, [ctx_p, C.c_int, u64p]),
     "epv_halo_record_bytes": (C.c_int, [ctx_p, u64p]),

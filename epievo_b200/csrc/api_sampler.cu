@@ -1,5 +1,6 @@
 // api_sampler.cu -- reset / sweep / run_mcmc / sufficient statistics / rescale.
 #include <cstring>
+#include <vector>
 
 #include "../../include/epievo_b200.h"
 #include "context.h"
@@ -237,6 +238,29 @@ int epv_scale_jump_times(epv_ctx *c, const double *new_branches) {
   c->tri_valid = false; c->stats_valid = false;
   EPV_CUDA(c, cudaGetLastError());
   return 0;
+}
+
+int epv_mcem_iteration(epv_ctx *c, uint64_t burn_in, uint64_t batch, uint64_t seed, uint64_t first_sweep,
+                       int optimize_branches, double param_tol, double *rates, double *T,
+                       double *branches, double *baseline, double *acc_rate, double *llh) {
+  if (!c) return 1;
+  if (!c->n_sites) return fail(c, "no paths loaded");
+  for (int b = 1; b < c->n_nodes; ++b)
+    if (branches[b] != c->h_branch[b])
+      return fail(c, "epv_mcem_iteration: branches differ from the context's tree (paths' tot_time)");
+  if (int r = epv_set_model(c, rates, T)) return r;          // reset follows from the new model
+  std::vector<double> J((size_t)c->n_nodes*8), D((size_t)c->n_nodes*8);
+  if (int r = epv_run_mcmc(c, burn_in, batch, seed, first_sweep, J.data(), D.data(), acc_rate)) return r;
+  double bl[4];
+  if (!optimize_branches) {                                  // epievo_est_params_histories.cpp:254-257
+    *llh = epv_estimate_rates((uint64_t)c->n_nodes, J.data(), D.data(), param_tol, rates, T, bl);
+    epv_set_one_change(rates, (uint64_t)c->n_nodes, branches);
+  }
+  else                                                       // :259-262
+    *llh = epv_estimate_rates_and_branches((uint64_t)c->n_nodes, J.data(), D.data(), param_tol, rates,
+                                           branches, T, bl);
+  if (baseline) for (int i = 0; i < 4; ++i) baseline[i] = bl[i];
+  return epv_scale_jump_times(c, branches);                  // :264
 }
 
 uint64_t epv_launch_count(const epv_ctx *c) { return c ? c->launches : 0; }

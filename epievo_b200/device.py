@@ -147,6 +147,17 @@ class Context:
                                            _d(D), C.byref(n)))
         return J.reshape(-1, 8), D.reshape(-1, 8), n.value
 
+    def mcem_iteration(self, burn_in, batch, seed, first_sweep, rates, T, branches,
+                       optimize_branches=False, param_tol=1e-10):
+        """One device-resident MCEM iteration; returns the updated (rates, T, branches,
+        baseline, acc_rate, llh)."""
+        r, t, br, bl = _f64(rates).copy(), _f64(T).copy(), _f64(branches).copy(), np.zeros(4)
+        acc, llh = C.c_double(), C.c_double()
+        self._ck(self.lib.epv_mcem_iteration(self.h, burn_in, batch, seed, first_sweep,
+                                             int(optimize_branches), param_tol, _d(r), _d(t), _d(br),
+                                             _d(bl), C.byref(acc), C.byref(llh)))
+        return r, t, br, bl, acc.value, llh.value
+
     # -- multi-GPU halo exchange (device buffers given as raw addresses) ------------------
     def halo_record_bytes(self) -> int:
         n = C.c_uint64()

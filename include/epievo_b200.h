@@ -111,6 +111,18 @@ int epv_llh_grad(epv_ctx *ctx, const double *rates, double *llh, double *grad);
  * lengths become new_branches. */
 int epv_scale_jump_times(epv_ctx *ctx, const double *new_branches);
 
+/* One whole MCEM iteration with the paths RESIDENT on the device -- replaces the body of the
+ * loop at prog/epievo_est_params_histories.cpp:239-264: reset, run_mcmc (E-step), the M-step
+ * (estimate_rates + set_one_change_per_site_per_unit_time, or estimate_rates_and_branches
+ * when optimize_branches != 0) and scale_jump_times.  rates[8], T[4] and branches[n_nodes]
+ * are the current model / tree on entry and the updated ones on return; baseline[4]
+ * receives the stationary baseline (may be NULL).  Paths never leave the GPU; call
+ * epv_download_paths when the reference would write its local-paths file. */
+int epv_mcem_iteration(epv_ctx *ctx, uint64_t burn_in, uint64_t batch, uint64_t seed,
+                       uint64_t first_sweep, int optimize_branches, double param_tol,
+                       double *rates, double *T, double *branches, double *baseline,
+                       double *acc_rate, double *llh);
+
 /* ---- multi-GPU building blocks (see epv_set_shard) --------------------------------- */
 /* One stride-3 colour pass (colour 0,1,2) of sweep sweep_idx over this shard's sites;
  * epv_sweep is three of these.  A sharded driver exchanges halos between passes. */
