@@ -19,6 +19,7 @@
 // costs one staging round trip of the accepted proposals (a few % of the row bytes).
 #include "kernels.h"
 #include "mh_flat.cuh"
+#include "scan.cuh"
 
 namespace epv {
 
@@ -29,14 +30,18 @@ constexpr uint32_t STG_REJECTED = 0xffffffffu, STG_EMPTY = 0xfffffffeu;
 __device__ __forceinline__ int stage_header_words(int n_br) { return (n_br + 3) >> 2; }
 
 #ifndef EPV_MH_MINBLOCKS
-#define EPV_MH_MINBLOCKS 5      // <= 96 registers; measured best of 1/5/6/8 (within 3 %)
+#define EPV_MH_MINBLOCKS 4      // <= 128 registers; measured best of 3/4/5 (5.5 / 6.2 / 6.5 ms)
 #endif
+
+// jump-queue slots per thread (shared memory: 24 B each)
+__host__ __device__ constexpr int mh_qcap(int maxn) { return maxn <= 16 ? 8 : maxn <= 64 ? 16 : 24; }
 
 template <int MAXN, int MAXJ, bool HALO>
 __global__ void __launch_bounds__(MH_THREADS, EPV_MH_MINBLOCKS)
 mh_update_kernel(const PassArgs a) {
   __shared__ ModelParams s_mp;
   __shared__ CtxTables s_tb;
+  extern __shared__ unsigned long long s_dyn[];    // [MH_THREADS*QCAP] QSlot, then [MH_THREADS] int
   const int t = threadIdx.x, lane = t & 31;
   const int n_br = a.tree.n_nodes - 1;
   if (t == 0) s_mp = a.mp;
@@ -47,8 +52,10 @@ mh_update_kernel(const PassArgs a) {
   const int64_t gsite = a.global0 + (int64_t)st;
 
   // interval stack / jump queue capacities grow with the tree (expected use ~ 0.1 / 0.07 per branch)
-  constexpr int PB = MAXN <= 16 ? 16 : MAXN/2, QCAP = MAXN <= 16 ? 8 : MAXN/4;
+  constexpr int PB = MAXN <= 16 ? 16 : MAXN/2, QCAP = mh_qcap(MAXN);
   FlatScratch<MAXN, PB, QCAP> S;
+  S.queue = reinterpret_cast<QSlot *>(s_dyn) + t*QCAP;
+  S.excl = reinterpret_cast<int *>(reinterpret_cast<QSlot *>(s_dyn) + MH_THREADS*QCAP) + (t & ~31);
   double pj_local[MAXJ];
   uint16_t pn[MAXN];
   uint8_t pend[MAXN];
@@ -114,54 +121,6 @@ mh_update_kernel(const PassArgs a) {
 }
 
 // ---- CSR re-compaction ------------------------------------------------------------------
-constexpr unsigned long long FLAG_AGG = 1ull << 32, FLAG_INC = 2ull << 32;
-
-__device__ __forceinline__ unsigned long long
-ld_desc(const unsigned long long *p) {
-  unsigned long long v;
-  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void
-st_desc(unsigned long long *p, unsigned long long v) {
-  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
-}
-
-// Exclusive prefix of this tile's total for one branch; executed by a full warp.
-__device__ __forceinline__ uint32_t
-tile_base(unsigned long long *desc, uint32_t tile, uint32_t epoch, uint32_t total,
-          int lane) {
-  const unsigned long long tag = (unsigned long long)epoch << 34;
-  if (tile == 0) {
-    if (lane == 0) st_desc(desc, tag | FLAG_INC | total);
-    return 0;
-  }
-  if (lane == 0) st_desc(desc + tile, tag | FLAG_AGG | total);
-  uint32_t base = 0;
-  int64_t look = (int64_t)tile - 1;
-  for (;;) {
-    const int64_t idx = look - lane;
-    unsigned long long d;
-    bool ready;
-    for (unsigned ns = 32;; ns = ns < 1024 ? 2*ns : ns) {
-      d = idx >= 0 ? ld_desc(desc + idx) : (tag | FLAG_INC);
-      ready = (d >> 34) == epoch && (d & (FLAG_AGG | FLAG_INC)) != 0;
-      if (!__any_sync(0xffffffffu, !ready)) break;
-      __nanosleep(ns);            // back off: a spinning warp must not steal issue slots
-    }
-    const unsigned inc = __ballot_sync(0xffffffffu, (d & FLAG_INC) != 0);
-    const int first = inc ? __ffs(inc) - 1 : 32;
-    uint32_t v = lane <= first ? (uint32_t)d : 0u;
-    v = warp_sum(v);
-    base += v;
-    if (inc) break;
-    look -= 32;
-  }
-  if (lane == 0) st_desc(desc + tile, tag | FLAG_INC | (base + total));
-  return base;
-}
-
-
 // Thread t of tile k owns the 4 consecutive CSR rows R = 4*(k*RB_THREADS + t) .. R+3 of
 // every branch (offsets move as one 16-byte vector).  Rows whose site has the pass's colour
 // take their new length / jump times from the staging blob when the update was accepted.
@@ -295,10 +254,15 @@ template <int MAXN, int MAXJ>
 static void
 launch_update_t(const PassArgs &a, cudaStream_t st) {
   const unsigned blocks = (unsigned)((a.n_groups + MH_THREADS - 1)/MH_THREADS);
-  if (a.in.own_lo == 0 && a.in.own_hi == a.in.n_local)
-    mh_update_kernel<MAXN, MAXJ, false><<<blocks, MH_THREADS, 0, st>>>(a);
-  else
-    mh_update_kernel<MAXN, MAXJ, true><<<blocks, MH_THREADS, 0, st>>>(a);
+  const size_t smem = (size_t)MH_THREADS*mh_qcap(MAXN)*sizeof(QSlot) + MH_THREADS*sizeof(int);
+  if (a.in.own_lo == 0 && a.in.own_hi == a.in.n_local) {
+    cudaFuncSetAttribute(mh_update_kernel<MAXN, MAXJ, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    mh_update_kernel<MAXN, MAXJ, false><<<blocks, MH_THREADS, smem, st>>>(a);
+  }
+  else {
+    cudaFuncSetAttribute(mh_update_kernel<MAXN, MAXJ, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    mh_update_kernel<MAXN, MAXJ, true><<<blocks, MH_THREADS, smem, st>>>(a);
+  }
 }
 
 void

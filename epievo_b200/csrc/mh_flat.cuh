@@ -99,33 +99,102 @@ load_lmr(const PathView &pv, const StateWin<WORDS> &sw, int bi, uint64_t site,
   }
 }
 
-struct QItem { double t_off, len; int v; int code; };   // code: ctx | cur<<3 | end<<4
+// One queued interval that needs jump times; lives in SHARED memory so that any lane of
+// the warp can sample it.  Pending: a = start time within the branch, b = length,
+// meta = v | ctx<<8 | cur<<11 | end<<12 | (per-site item number)<<16.  Done: a, b = the
+// (at most two) jump times, meta = v | count<<16 | Q_DONE.
+struct QSlot { double a, b; unsigned meta; unsigned pad; };
+constexpr unsigned Q_DONE = 1u << 31;
 
 template <int MAXN, int PB, int QCAP>
 struct FlatScratch {
   double q[2*MAXN];
   double hb[MAXN];
   double stk[3*PB];
-  QItem queue[QCAP];
+  QSlot *queue;        // this thread's QCAP slots in shared memory
+  int *excl;           // this warp's 32 prefix counts in shared memory
 };
 
-// Drain the queue of intervals that need jump times (FIFO keeps pj in branch/time order).
-template <int QCAP>
+// Philox stream of the k-th queued interval of a site: node index 2 + k (0 = accept draw,
+// 1 = downward pass), so the result does not depend on which lane samples it.
 __device__ __forceinline__ int
-drain_queue(const ModelParams &mp, QItem *queue, int &qn, Philox &rng, Proposal &pr, int total) {
+sample_slot(const ModelParams &mp, const QSlot &it, uint64_t seed, uint32_t sweep, uint64_t gsite,
+            double *out, int n, int cap) {
+  const int ctx = (it.meta >> 8) & 7, cur = (it.meta >> 11) & 1, end = (it.meta >> 12) & 1;
+  Philox rng; rng.init(seed, sweep, gsite, 2u + ((it.meta >> 16) & 0x7fffu));
+  return end_cond_sample(mp.rate[ctx], mp.rate[ctx | 2], cur, end, it.b, it.a, rng, out, n, cap,
+                         cur == end);
+}
+
+// Owner-side collection of the queue (FIFO keeps pj in branch / time order): slots already
+// sampled by some lane are copied, the others are sampled here with their own stream.
+__device__ __forceinline__ int
+collect_queue(const ModelParams &mp, QSlot *queue, int &qn, uint64_t seed, uint32_t sweep,
+              uint64_t gsite, Proposal &pr, int total) {
   for (int k = 0; k < qn; ++k) {
-    const QItem it = queue[k];
-    const int ctx = it.code & 7, cur = (it.code >> 3) & 1, end = (it.code >> 4) & 1;
+    const QSlot it = queue[k];
+    const int v = it.meta & 0xff;
     const int before = total;
-    total = end_cond_sample(mp.rate[ctx], mp.rate[ctx | 2], cur, end, it.len, it.t_off, rng,
-                            pr.pj, total, pr.cap, cur == end);
-    if (total < 0) return total;
-    const int add = total - before + pr.pn[it.v];
+    if (it.meta & Q_DONE) {
+      const int cnt = (it.meta >> 16) & 3;
+      if (total + cnt > pr.cap) return -1;
+      pr.pj[total] = it.a;
+      if (cnt > 1) pr.pj[total + 1] = it.b;
+      total += cnt;
+    }
+    else {
+      total = sample_slot(mp, it, seed, sweep, gsite, pr.pj, total, pr.cap);
+      if (total < 0) return total;
+    }
+    const int add = total - before + pr.pn[v];
     if (add > 65535) return -1;
-    pr.pn[it.v] = (uint16_t)add;
+    pr.pn[v] = (uint16_t)add;
   }
   qn = 0;
   return total;
+}
+
+// Warp-cooperative sampling of every pending slot of the warp's 32 queues: the slots are
+// numbered through a prefix sum of the queue lengths and dealt out 32 at a time, one per
+// lane, so the rare jump-time work runs with the lanes full instead of 2-4 active.
+// Results with more than two jumps stay pending (the owner samples them in collect_queue
+// with the same stream => same result).  Warp-synchronous.
+template <int QCAP>
+__device__ __forceinline__ void
+coop_sample(const ModelParams &mp, QSlot *queue, int *excl, int qn, uint64_t seed, uint32_t sweep,
+            uint64_t gsite) {
+  constexpr unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  int incl = qn;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int up = __shfl_up_sync(FULL, incl, o);
+    if (lane >= o) incl += up;
+  }
+  const int T = __shfl_sync(FULL, incl, 31);
+  excl[lane] = incl - qn;
+  __syncwarp();
+  QSlot *warp_q = queue - lane*QCAP;                 // lane 0's slots; lane L's are + L*QCAP
+  const uint32_t g_lo = (uint32_t)gsite, g_hi = (uint32_t)(gsite >> 32);
+  for (int base = 0; base < T; base += 32) {
+    const int j = base + lane;
+    int owner = 0;
+#pragma unroll
+    for (int st = 16; st > 0; st >>= 1)
+      if (owner + st < 32 && excl[owner + st] <= j) owner += st;
+    const uint64_t og = ((uint64_t)__shfl_sync(FULL, g_hi, owner) << 32) | __shfl_sync(FULL, g_lo, owner);
+    if (j < T) {
+      QSlot *slot = warp_q + owner*QCAP + (j - excl[owner]);
+      const QSlot it = *slot;
+      double out[2];
+      const int n = sample_slot(mp, it, seed, sweep, og, out, 0, 2);
+      if (n > 0) {
+        slot->a = out[0]; slot->b = n > 1 ? out[1] : 0.0;
+        slot->meta = (it.meta & 0xffu) | ((unsigned)n << 16) | Q_DONE;
+      }
+    }
+  }
+  __syncwarp();
 }
 
 // Returns 1 accepted, 0 rejected (or inactive lane), -1 proposal buffer too small (rerun
@@ -193,7 +262,7 @@ mh_site_flat(bool active, const ModelParams &mp, const CtxTables &tb, const Site
   // ---- 2. downward pass, flat over (branch, interval) -----------------------------
   Philox rng; rng.init(seed, sweep, gsite, 1u);
   pr.pend[0] = active ? (uint8_t)sw.bit(0, 1) : 0;
-  int total = 0, qn = 0;
+  int total = 0, qn = 0, q_total = 0;
   {
     int v = (active && status > 0) ? 1 : n_nodes, prev = 0, i = 0;
     FwdMerge m;
@@ -227,9 +296,11 @@ mh_site_flat(bool active, const ModelParams &mp, const CtxTables &tb, const Site
         need_jumps = !(u_jump*(prev ? P11 : P00) < ea);
       }
       if (need_jumps) {
-        if (qn == QCAP) total = drain_queue<QCAP>(mp, S.queue, qn, rng, pr, total);
+        if (qn == QCAP) total = collect_queue(mp, S.queue, qn, seed, sweep, gsite, pr, total);
         if (total < 0) { status = total; v = n_nodes; continue; }
-        QItem it; it.t_off = passed; it.len = len; it.v = v; it.code = ctx | (prev << 3) | (e << 4);
+        QSlot it; it.a = passed; it.b = len; it.pad = 0;
+        it.meta = (unsigned)v | (unsigned)ctx << 8 | (unsigned)prev << 11 | (unsigned)e << 12 |
+                  ((unsigned)(q_total++) & 0x7fffu) << 16;
         S.queue[qn++] = it;
       }
       passed += len; prev = e; ++i;
@@ -237,8 +308,10 @@ mh_site_flat(bool active, const ModelParams &mp, const CtxTables &tb, const Site
     }
   }
   // ---- 3. jump times of the queued intervals ---------------------------------------
+  if (status <= 0) qn = 0;
+  coop_sample<QCAP>(mp, S.queue, S.excl, qn, seed, sweep, gsite);
   if (status > 0) {
-    total = drain_queue<QCAP>(mp, S.queue, qn, rng, pr, total);
+    total = collect_queue(mp, S.queue, qn, seed, sweep, gsite, pr, total);
     if (total < 0) status = total;
   }
   __syncwarp(FULL);
