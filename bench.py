@@ -161,6 +161,8 @@ def main():
     ap.add_argument("--cpu-procs", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--exchange", choices=("compact", "csr"), default="compact",
+                    help="host exchange format of the e2e leg (u16 row codes, or 9-byte CSR rows)")
     args = ap.parse_args()
     if not args.sites:
         args.sites = DEFAULT_SITES[args.workload]
@@ -218,6 +220,8 @@ def main():
     h_init.numpy()[:] = ps.init_state
     h_off.numpy()[:] = ps.row_off.view(np.int64)
     h_jmp.numpy()[:ps.jumps.size] = ps.jumps
+    h_code = torch.empty(n_rows, dtype=torch.int16, pin_memory=True)   # compact format: u16 codes
+    nj_host = int(ps.jumps.size)
     tot_time = ps.tot_time.copy()
     del ps
 
@@ -284,21 +288,33 @@ def main():
         n_sites_, n_nodes_, nj = ctx.paths_size()
         if nj > jcap:
             raise SystemExit("bench.py: pinned jump buffer too small")
-        ctx.download_raw(h_init.data_ptr(), h_off.data_ptr(), h_jmp.data_ptr())
+        compact = args.exchange == "compact"
+        if compact:
+            nj_host = ctx.download_compact_raw(h_code.data_ptr(), h_jmp.data_ptr(), jcap)
+        else:
+            ctx.download_raw(h_init.data_ptr(), h_off.data_ptr(), h_jmp.data_ptr())
         h2d = d2h = 0
         barrier()
         e0.record(stream)
         for _ in range(args.steps):
-            nj_in = int(h_off[n_rows].item())
-            ctx.upload_raw(n, tree.n_nodes, h_init.data_ptr(), h_off.data_ptr(), h_jmp.data_ptr(), tot_time)
+            if compact:
+                nj_in = nj_host
+                ctx.upload_compact_raw(n, tree.n_nodes, h_code.data_ptr(), h_jmp.data_ptr(), nj_in, tot_time)
+            else:
+                nj_in = int(h_off[n_rows].item())
+                ctx.upload_raw(n, tree.n_nodes, h_init.data_ptr(), h_off.data_ptr(), h_jmp.data_ptr(), tot_time)
             J, D, acc2 = e_step(sweep_no)
             sweep_no += sweeps
-            _, _, nj_out = ctx.paths_size()
-            if nj_out > jcap:
-                raise SystemExit("bench.py: pinned jump buffer too small")
-            ctx.download_raw(h_init.data_ptr(), h_off.data_ptr(), h_jmp.data_ptr())
-            h2d += n_rows + 8 * (n_rows + 1) + 8 * nj_in
-            d2h += n_rows + 8 * (n_rows + 1) + 8 * nj_out + 2 * 8 * 8 * tree.n_nodes
+            if compact:
+                nj_host = nj_out = ctx.download_compact_raw(h_code.data_ptr(), h_jmp.data_ptr(), jcap)
+            else:
+                _, _, nj_out = ctx.paths_size()
+                if nj_out > jcap:
+                    raise SystemExit("bench.py: pinned jump buffer too small")
+                ctx.download_raw(h_init.data_ptr(), h_off.data_ptr(), h_jmp.data_ptr())
+            per_row = 2 * n_rows if compact else n_rows + 8 * (n_rows + 1)
+            h2d += per_row + 8 * nj_in
+            d2h += per_row + 8 * nj_out + 2 * 8 * 8 * tree.n_nodes
         e1.record(stream)
         barrier()
         t2 = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
@@ -307,7 +323,9 @@ def main():
         e2e = {"value": updates_per_step * args.steps / (float(t2.item()) * 1e-3), "unit": UNIT,
                "h2d_bytes_per_step": h2d // args.steps, "d2h_bytes_per_step": d2h // args.steps,
                "ms_per_step": float(t2.item()) / args.steps,
-               "call": "epv_upload_paths + epv_run_mcmc + epv_download_paths (pinned host buffers)"}
+               "call": ("epv_upload_paths_compact + epv_run_mcmc + epv_download_paths_compact"
+                        if compact else "epv_upload_paths + epv_run_mcmc + epv_download_paths")
+                       + " (pinned host buffers)"}
 
     # ---- roofline of the dominant kernel -----------------------------------------------
     peaks_file = os.path.join(ROOT, "MEASURED_PEAKS.json")

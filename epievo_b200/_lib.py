@@ -15,6 +15,7 @@ dp = C.POINTER(C.c_double)
 u64p = C.POINTER(C.c_uint64)
 u32p = C.POINTER(C.c_uint32)
 u8p = C.POINTER(C.c_uint8)
+u16p = C.POINTER(C.c_uint16)
 ctx_p = C.c_void_p
 u64 = C.c_uint64
 
@@ -31,6 +32,8 @@ SIGNATURES = {
     "epv_upload_paths": (C.c_int, [ctx_p, u64, u64, u8p, u64p, dp, dp]),
     "epv_paths_size": (C.c_int, [ctx_p, u64p, u64p, u64p]),
     "epv_download_paths": (C.c_int, [ctx_p, u8p, u64p, dp, dp]),
+    "epv_upload_paths_compact": (C.c_int, [ctx_p, u64, u64, u16p, dp, u64, dp]),
+    "epv_download_paths_compact": (C.c_int, [ctx_p, u16p, dp, u64, u64p, dp]),
     "epv_reset": (C.c_int, [ctx_p]),
     "epv_sweep": (C.c_int, [ctx_p, u64, u64, u64p]),
     "epv_run_mcmc": (C.c_int, [ctx_p, u64, u64, u64, u64, dp, dp, dp]),

@@ -27,7 +27,7 @@ void free_paths(epv_ctx *c) {
   c->d_hcnt = nullptr; c->d_hjmp = nullptr; c->d_stage_init = nullptr; c->d_stage_off = nullptr;
   c->d_jbase = c->d_jcap = nullptr; c->d_state = nullptr; c->d_tri = nullptr;
   c->d_desc = nullptr;
-  c->n_sites = 0; c->tri_valid = false; c->stats_valid = false;
+  c->n_sites = 0; c->tri_valid = false; c->stats_valid = false; c->h_jcap.clear();
 }
 
 int check_device_flags(epv_ctx *c) {
@@ -129,7 +129,8 @@ int epv_synchronize(epv_ctx *c) {
 int epv_set_tree(epv_ctx *c, uint64_t n_nodes, const uint64_t *subtree_sizes,
                  const uint64_t *parent_ids, const double *branches) {
   if (!c) return 1;
-  if (n_nodes < 2 || n_nodes > 256) return fail(c, "tree must have 2..256 nodes");
+  // the CSR rebuild keeps one u32 per (branch, thread) in shared memory: (n_nodes-1) KB <= 227 KB
+  if (n_nodes < 2 || n_nodes > 224) return fail(c, "tree must have 2..224 nodes");
   for (uint64_t v = 1; v < n_nodes; ++v) {
     if (parent_ids[v] >= v) return fail(c, "tree is not in preorder (parent_ids[v] >= v)");
     if (!(branches[v] > 0.0)) return fail(c, "branch lengths must be positive");

@@ -102,11 +102,10 @@ static int64_t slot_site(const epv_ctx *c, int k) {
 
 }  // namespace epv
 
-extern "C" {
+namespace epv {
 
-int epv_upload_paths(epv_ctx *c, uint64_t n_sites, uint64_t n_nodes, const uint8_t *init_state,
-                     const uint64_t *row_off, const double *jumps, const double *tot_time) {
-  if (!c) return 1;
+// Argument checks shared by the two upload entry points; fills in the default shard.
+static int check_upload(epv_ctx *c, uint64_t n_sites, uint64_t n_nodes, const double *tot_time) {
   if (!c->n_nodes) return fail(c, "epv_set_tree must be called before epv_upload_paths");
   if ((int)n_nodes != c->n_nodes) return fail(c, "paths and tree disagree on the number of nodes");
   if (n_sites < 3) return fail(c, "need at least 3 sites");
@@ -116,11 +115,71 @@ int epv_upload_paths(epv_ctx *c, uint64_t n_sites, uint64_t n_nodes, const uint8
   }
   if (n_sites != c->site_end - c->site_begin + c->halo_lo + c->halo_hi)
     return fail(c, "n_sites does not match the shard set with epv_set_shard");
-  const int n_br = c->n_nodes - 1;
   for (int b = 1; b < c->n_nodes; ++b)
     if (tot_time[b] != c->h_branch[b])
       return fail(c, "paths' tot_time differs from the tree's branch length (the reference "
                      "asserts equality, Segment.cpp:76); rescale the paths or the tree");
+  return 0;
+}
+
+// Everything whose size depends only on (n_sites, n_nodes); kept across uploads of the
+// same shape.
+static int ensure_shape(epv_ctx *c, uint64_t n_sites) {
+  if (c->n_sites == n_sites && c->d_off[0]) return 0;
+  free_paths(c);
+  c->h_jcap.clear();
+  const int n_br = c->n_nodes - 1;
+  const uint64_t n_own = n_sites - c->halo_lo - c->halo_hi;
+  c->n_sites = n_sites;
+  c->W = 1;                                         // bytes of state bits per site, a power of two
+  while (c->W*8 < c->n_nodes) c->W *= 2;            // so that <= 64 nodes are one aligned load
+  c->off_pitch = (n_own + 1 + 4 + 31) & ~31ull;     // room for the rebuild kernel's 16-byte vectors
+  c->n_tiles = (uint32_t)((n_own + 1 + RB_TILE_ROWS - 1)/RB_TILE_ROWS);
+  for (int k = 0; k < 2; ++k)
+    EPV_CUDA(c, cudaMalloc(&c->d_off[k], (size_t)n_br*c->off_pitch*sizeof(uint32_t)));
+  EPV_CUDA(c, cudaMalloc(&c->d_jbase, n_br*sizeof(uint64_t)));
+  EPV_CUDA(c, cudaMalloc(&c->d_jcap, n_br*sizeof(uint64_t)));
+  EPV_CUDA(c, cudaMalloc(&c->d_state, (size_t)n_sites*c->W));
+  EPV_CUDA(c, cudaMalloc(&c->d_tri, n_sites*sizeof(double)));
+  EPV_CUDA(c, cudaMalloc(&c->d_desc, (size_t)n_br*c->n_tiles*sizeof(unsigned long long)));
+  EPV_CUDA(c, cudaMalloc(&c->d_hcnt, (size_t)2*HALO_W*n_br*sizeof(uint16_t)));
+  EPV_CUDA(c, cudaMalloc(&c->d_hjmp, (size_t)2*HALO_W*n_br*HALO_K*sizeof(double)));
+  const uint64_t n_rows = (uint64_t)c->n_nodes*n_sites;
+  EPV_CUDA(c, cudaMalloc(&c->d_stage_init, n_rows));
+  EPV_CUDA(c, cudaMalloc(&c->d_stage_off, (n_rows + 1)*sizeof(unsigned long long)));
+  EPV_CUDA(c, cudaMemsetAsync(c->d_desc, 0, (size_t)n_br*c->n_tiles*sizeof(unsigned long long), c->stream));
+  c->epoch = 0;
+  return 0;
+}
+
+// Jump buffers (+ the proposal staging blob): reallocated only when a branch no longer fits.
+static int ensure_jumps(epv_ctx *c, const std::vector<uint64_t> &count) {
+  const int n_br = c->n_nodes - 1;
+  bool fits = (int)c->h_jcap.size() == n_br && c->d_jmp[0];
+  for (int bi = 0; fits && bi < n_br; ++bi) fits = 4*count[bi] <= 3*c->h_jcap[bi];
+  for (int bi = 0; bi < n_br; ++bi)
+    if (count[bi] > 0xfffffff0ull) return fail(c, "a branch holds more than 2^32 jumps on one GPU; use more shards");
+  if (fits) return 0;
+  for (int k = 0; k < 2; ++k) { cudaFree(c->d_jmp[k]); c->d_jmp[k] = nullptr; }
+  std::vector<uint64_t> cap(n_br);
+  for (int bi = 0; bi < n_br; ++bi) cap[bi] = capacity_for(count[bi], c->n_own());
+  if (int r = alloc_jumps(c, cap, c->d_jmp, c->h_jbase, c->jmp_total_cap)) return r;
+  c->h_jcap = cap;
+  if (int r = alloc_stage(c)) return r;
+  EPV_CUDA(c, cudaMemcpyAsync(c->d_jbase, c->h_jbase.data(), n_br*sizeof(uint64_t), cudaMemcpyHostToDevice, c->stream));
+  EPV_CUDA(c, cudaMemcpyAsync(c->d_jcap, c->h_jcap.data(), n_br*sizeof(uint64_t), cudaMemcpyHostToDevice, c->stream));
+  return 0;
+}
+
+}  // namespace epv
+
+extern "C" {
+
+int epv_upload_paths(epv_ctx *c, uint64_t n_sites, uint64_t n_nodes, const uint8_t *init_state,
+                     const uint64_t *row_off, const double *jumps, const double *tot_time) {
+  if (!c) return 1;
+  if (int r = check_upload(c, n_sites, n_nodes, tot_time)) return r;
+  const int n_br = c->n_nodes - 1;
   if (row_off[0] != 0 || row_off[n_sites] != row_off[0]) return fail(c, "root rows must be empty");
   const uint64_t own_lo = c->halo_lo, own_hi = n_sites - c->halo_hi, n_own = own_hi - own_lo;
   std::vector<uint64_t> count(n_br), first(n_br);
@@ -129,42 +188,10 @@ int epv_upload_paths(epv_ctx *c, uint64_t n_sites, uint64_t n_nodes, const uint8
     if (row_off[r + n_sites] < row_off[r]) return fail(c, "row_off must be non-decreasing");
     first[bi] = row_off[r + own_lo];
     count[bi] = row_off[r + own_hi] - first[bi];
-    if (count[bi] > 0xfffffff0ull) return fail(c, "a branch holds more than 2^32 jumps on one GPU; use more shards");
   }
   EPV_CUDA(c, cudaStreamSynchronize(c->stream));
-
-  // (re)allocate only when the shape changed or a branch no longer fits
-  bool fits = c->n_sites == n_sites && c->d_off[0] && (int)c->h_jcap.size() == n_br;
-  for (int bi = 0; fits && bi < n_br; ++bi) fits = 4*count[bi] <= 3*c->h_jcap[bi];
-  if (!fits) {
-    free_paths(c);
-    std::vector<uint64_t> cap(n_br);
-    for (int bi = 0; bi < n_br; ++bi) cap[bi] = capacity_for(count[bi], n_own);
-    c->n_sites = n_sites;
-    c->W = 1;                                         // bytes of state bits per site, a power of two
-    while (c->W*8 < c->n_nodes) c->W *= 2;            // so that <= 64 nodes are one aligned load
-    c->off_pitch = (n_own + 1 + 4 + 31) & ~31ull;     // room for the rebuild kernel's 16-byte vectors
-    c->n_tiles = (uint32_t)((n_own + 1 + RB_TILE_ROWS - 1)/RB_TILE_ROWS);
-    if (int r = alloc_jumps(c, cap, c->d_jmp, c->h_jbase, c->jmp_total_cap)) return r;
-    c->h_jcap = cap;
-    for (int k = 0; k < 2; ++k)
-      EPV_CUDA(c, cudaMalloc(&c->d_off[k], (size_t)n_br*c->off_pitch*sizeof(uint32_t)));
-    EPV_CUDA(c, cudaMalloc(&c->d_jbase, n_br*sizeof(uint64_t)));
-    EPV_CUDA(c, cudaMalloc(&c->d_jcap, n_br*sizeof(uint64_t)));
-    EPV_CUDA(c, cudaMalloc(&c->d_state, (size_t)n_sites*c->W));
-    EPV_CUDA(c, cudaMalloc(&c->d_tri, n_sites*sizeof(double)));
-    EPV_CUDA(c, cudaMalloc(&c->d_desc, (size_t)n_br*c->n_tiles*sizeof(unsigned long long)));
-    EPV_CUDA(c, cudaMalloc(&c->d_hcnt, (size_t)2*HALO_W*n_br*sizeof(uint16_t)));
-    EPV_CUDA(c, cudaMalloc(&c->d_hjmp, (size_t)2*HALO_W*n_br*HALO_K*sizeof(double)));
-    const uint64_t n_rows = n_nodes*n_sites;
-    EPV_CUDA(c, cudaMalloc(&c->d_stage_init, n_rows));
-    EPV_CUDA(c, cudaMalloc(&c->d_stage_off, (n_rows + 1)*sizeof(unsigned long long)));
-    if (int r = alloc_stage(c)) return r;
-    EPV_CUDA(c, cudaMemsetAsync(c->d_desc, 0, (size_t)n_br*c->n_tiles*sizeof(unsigned long long), c->stream));
-    c->epoch = 0;
-    EPV_CUDA(c, cudaMemcpyAsync(c->d_jbase, c->h_jbase.data(), n_br*sizeof(uint64_t), cudaMemcpyHostToDevice, c->stream));
-    EPV_CUDA(c, cudaMemcpyAsync(c->d_jcap, c->h_jcap.data(), n_br*sizeof(uint64_t), cudaMemcpyHostToDevice, c->stream));
-  }
+  if (int r = ensure_shape(c, n_sites)) return r;
+  if (int r = ensure_jumps(c, count)) return r;
   c->cur = 0; c->tri_valid = false; c->stats_valid = false;
 
   // raw host arrays -> device staging -> layout conversion on the device
@@ -214,6 +241,31 @@ static int branch_jump_layout(epv_ctx *c, std::vector<uint64_t> &own, std::vecto
   return 0;
 }
 
+// Jump times of every branch to the host array: low-halo rows, owned rows, high-halo rows.
+static int copy_jumps_out(epv_ctx *c, const std::vector<uint64_t> &own, const std::vector<uint16_t> &hc,
+                          const std::vector<double> &hj, const std::vector<uint64_t> &prefix,
+                          double *jumps) {
+  const int n_br = c->n_nodes - 1;
+  for (int bi = 0; bi < n_br; ++bi) {
+    double *dst = jumps + prefix[bi];
+    for (int k = 0; k < HALO_W; ++k)
+      if (slot_site(c, k) >= 0) {
+        const size_t row = (size_t)k*n_br + bi;
+        std::memcpy(dst, &hj[row*HALO_K], hc[row]*sizeof(double)); dst += hc[row];
+      }
+    if (own[bi])
+      EPV_CUDA(c, cudaMemcpyAsync(dst, c->d_jmp[c->cur] + c->h_jbase[bi], own[bi]*sizeof(double),
+                                  cudaMemcpyDeviceToHost, c->stream));
+    dst += own[bi];
+    for (int k = HALO_W; k < 2*HALO_W; ++k)
+      if (slot_site(c, k) >= 0) {
+        const size_t row = (size_t)k*n_br + bi;
+        std::memcpy(dst, &hj[row*HALO_K], hc[row]*sizeof(double)); dst += hc[row];
+      }
+  }
+  return 0;
+}
+
 int epv_paths_size(epv_ctx *c, uint64_t *n_sites, uint64_t *n_nodes, uint64_t *n_jumps) {
   if (!c) return 1;
   if (!c->n_sites) return fail(c, "no paths loaded");
@@ -255,27 +307,108 @@ int epv_download_paths(epv_ctx *c, uint8_t *init_state, uint64_t *row_off, doubl
   ++c->launches;
   EPV_CUDA(c, cudaMemcpyAsync(init_state, c->d_stage_init, n_rows, cudaMemcpyDeviceToHost, c->stream));
   EPV_CUDA(c, cudaMemcpyAsync(row_off, c->d_stage_off, (n_rows + 1)*sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
-  for (int bi = 0; bi < n_br; ++bi) {
-    double *dst = jumps + prefix[bi];
-    for (int k = 0; k < HALO_W; ++k)
-      if (slot_site(c, k) >= 0) {
-        const size_t row = (size_t)k*n_br + bi;
-        std::memcpy(dst, &hj[row*HALO_K], hc[row]*sizeof(double)); dst += hc[row];
-      }
-    if (own[bi])
-      EPV_CUDA(c, cudaMemcpyAsync(dst, c->d_jmp[c->cur] + c->h_jbase[bi], own[bi]*sizeof(double),
-                                  cudaMemcpyDeviceToHost, c->stream));
-    dst += own[bi];
-    for (int k = HALO_W; k < 2*HALO_W; ++k)
-      if (slot_site(c, k) >= 0) {
-        const size_t row = (size_t)k*n_br + bi;
-        std::memcpy(dst, &hj[row*HALO_K], hc[row]*sizeof(double)); dst += hc[row];
-      }
-  }
+  if (int r = copy_jumps_out(c, own, hc, hj, prefix, jumps)) return r;
   EPV_CUDA(c, cudaStreamSynchronize(c->stream));
   for (int b = 0; b < c->n_nodes; ++b) tot_time[b] = c->h_branch[b];
   EPV_CUDA(c, cudaGetLastError());
   return 0;
+}
+
+int epv_upload_paths_compact(epv_ctx *c, uint64_t n_sites, uint64_t n_nodes, const uint16_t *row_code,
+                             const double *jumps, uint64_t n_jumps, const double *tot_time) {
+  if (!c) return 1;
+  if (int r = check_upload(c, n_sites, n_nodes, tot_time)) return r;
+  const int n_br = c->n_nodes - 1;
+  if ((size_t)3*n_br > 4096) return fail(c, "too many branches");
+  const uint64_t own_lo = c->halo_lo, own_hi = n_sites - c->halo_hi, n_own = own_hi - own_lo;
+  EPV_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (int r = ensure_shape(c, n_sites)) return r;
+  c->cur = 0; c->tri_valid = false; c->stats_valid = false;
+
+  // codes -> device; per-branch totals come back so that the host can size the jump buffers
+  const uint64_t n_rows = n_nodes*n_sites;
+  uint16_t *d_code = reinterpret_cast<uint16_t *>(c->d_stage_off);
+  EPV_CUDA(c, cudaMemcpyAsync(d_code, row_code, n_rows*sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream));
+  launch_compact_totals(d_code, n_sites, n_br, own_lo, own_hi, c->d_mail, c->stream);
+  EPV_CUDA(c, cudaMemcpyAsync(c->h_mail, c->d_mail, (size_t)3*n_br*sizeof(unsigned long long),
+                              cudaMemcpyDeviceToHost, c->stream));
+  EPV_CUDA(c, cudaStreamSynchronize(c->stream));
+  std::vector<uint64_t> count(n_br), first(n_br);
+  uint64_t run = 0;
+  for (int bi = 0; bi < n_br; ++bi) {
+    first[bi] = run + c->h_mail[3*bi];
+    count[bi] = c->h_mail[3*bi + 1];
+    run = first[bi] + count[bi] + c->h_mail[3*bi + 2];
+  }
+  if (run != n_jumps) return fail(c, "the row codes' jump counts do not add up to n_jumps");
+  if (int r = ensure_jumps(c, count)) return r;
+
+  if (++c->epoch >= (1u << 30)) {
+    EPV_CUDA(c, cudaMemsetAsync(c->d_desc, 0, (size_t)n_br*c->n_tiles*sizeof(unsigned long long), c->stream));
+    c->epoch = 1;
+  }
+  launch_compact_import(d_code, n_sites, c->n_nodes, own_lo, n_own, c->d_off[0], c->off_pitch, c->d_state,
+                        c->W, c->d_desc, c->n_tiles, c->epoch, c->d_ticket, c->ticket_base, c->stream);
+  c->ticket_base += c->n_tiles;
+  c->launches += 2;
+  for (int bi = 0; bi < n_br; ++bi)
+    if (count[bi])
+      EPV_CUDA(c, cudaMemcpyAsync(c->d_jmp[0] + c->h_jbase[bi], jumps + first[bi],
+                                  count[bi]*sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  // halo sites (at most 2*HALO_W): state bits and the fixed-capacity halo store, from the host
+  std::vector<uint16_t> hc((size_t)2*HALO_W*n_br, 0);
+  std::vector<double> hj((size_t)2*HALO_W*n_br*HALO_K, 0.0);
+  std::vector<uint8_t> hs((size_t)2*HALO_W*c->W, 0);
+  for (int bi = -1; bi < n_br; ++bi) {
+    const uint16_t *row = row_code + (uint64_t)(bi + 1)*n_sites;
+    uint64_t lo = bi < 0 ? 0 : first[bi] - c->h_mail[3*bi], hi = bi < 0 ? 0 : first[bi] + count[bi];
+    for (int k = 0; k < 2*HALO_W; ++k) {
+      const int64_t s = slot_site(c, k);
+      if (s < 0) continue;
+      if (row[s] >> 15) hs[(size_t)k*c->W + (bi + 1)/8] |= (uint8_t)(1u << ((bi + 1) & 7));
+      if (bi < 0) continue;
+      const uint64_t n = row[s] & 0x7fffu;
+      if (n > HALO_K) return fail(c, "a halo row holds more jumps than the halo store's per-row capacity");
+      uint64_t &pos = k < HALO_W ? lo : hi;
+      hc[(size_t)k*n_br + bi] = (uint16_t)n;
+      std::memcpy(&hj[((size_t)k*n_br + bi)*HALO_K], jumps + pos, n*sizeof(double));
+      pos += n;
+    }
+  }
+  for (int k = 0; k < 2*HALO_W; ++k) {
+    const int64_t s = slot_site(c, k);
+    if (s >= 0)
+      EPV_CUDA(c, cudaMemcpyAsync(c->d_state + (uint64_t)s*c->W, &hs[(size_t)k*c->W], c->W,
+                                  cudaMemcpyHostToDevice, c->stream));
+  }
+  EPV_CUDA(c, cudaMemcpyAsync(c->d_hcnt, hc.data(), hc.size()*sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream));
+  EPV_CUDA(c, cudaMemcpyAsync(c->d_hjmp, hj.data(), hj.size()*sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  EPV_CUDA(c, cudaStreamSynchronize(c->stream));
+  EPV_CUDA(c, cudaGetLastError());
+  return 0;
+}
+
+int epv_download_paths_compact(epv_ctx *c, uint16_t *row_code, double *jumps, uint64_t jumps_cap,
+                               uint64_t *n_jumps, double *tot_time) {
+  if (!c) return 1;
+  if (!c->n_sites) return fail(c, "no paths loaded");
+  cudaSetDevice(c->device);
+  if (int r = check_device_flags(c)) return r;
+  const int n_br = c->n_nodes - 1;
+  std::vector<uint64_t> own, prefix; std::vector<uint16_t> hc; std::vector<double> hj;
+  if (int r = branch_jump_layout(c, own, hc, hj, prefix)) return r;
+  if (n_jumps) *n_jumps = prefix.back();
+  if (prefix.back() > jumps_cap) return fail(c, "jumps buffer too small (see *n_jumps / epv_paths_size)");
+  const uint64_t n_rows = (uint64_t)c->n_nodes*c->n_sites;
+  uint16_t *d_code = reinterpret_cast<uint16_t *>(c->d_stage_off);
+  launch_compact_export(c->view(c->cur), c->d_state, c->W, c->n_sites, c->n_nodes, d_code, c->d_err, c->stream);
+  ++c->launches;
+  EPV_CUDA(c, cudaMemcpyAsync(row_code, d_code, n_rows*sizeof(uint16_t), cudaMemcpyDeviceToHost, c->stream));
+  if (int r = copy_jumps_out(c, own, hc, hj, prefix, jumps)) return r;
+  EPV_CUDA(c, cudaStreamSynchronize(c->stream));
+  for (int b = 0; b < c->n_nodes; ++b) tot_time[b] = c->h_branch[b];
+  EPV_CUDA(c, cudaGetLastError());
+  return check_device_flags(c);
 }
 
 }  // extern "C"

@@ -89,6 +89,16 @@ void launch_export(const PathView &pv, const uint8_t *state, int W, uint64_t n_s
                    int n_nodes, const uint64_t *jprefix, uint8_t *h_init,
                    unsigned long long *h_off, cudaStream_t st);
 
+// compact host exchange format (kernels_compact.cu)
+void launch_compact_totals(const uint16_t *code, uint64_t n_sites, int n_br, uint64_t own_lo,
+                           uint64_t own_hi, unsigned long long *totals, cudaStream_t st);
+void launch_compact_import(const uint16_t *code, uint64_t n_sites, int n_nodes, uint64_t own_lo,
+                           uint64_t n_own, uint32_t *off, uint64_t pitch, uint8_t *state, int W,
+                           unsigned long long *desc, uint32_t n_tiles, uint32_t epoch,
+                           uint32_t *ticket, uint32_t ticket_base, cudaStream_t st);
+void launch_compact_export(const PathView &pv, const uint8_t *state, int W, uint64_t n_sites,
+                           int n_nodes, uint16_t *code, unsigned *err, cudaStream_t st);
+
 // ---- halo exchange (multi-GPU): one boundary site per side per colour pass -------------
 // Record (8-byte words): [0..2] tri_llh[s-1], [s], [s+1]; [3] global site index;
 // [4 .. 4+SW) state bytes; then n_br u16 jump counts packed in CW words; then

@@ -109,6 +109,41 @@ class Context:
             self.h, C.cast(init_ptr, L.u8p), C.cast(off_ptr, L.u64p), C.cast(jumps_ptr, L.dp),
             _d(tot)))
 
+    # compact exchange format: u16 row codes (count | init << 15) + jump times
+    def upload_paths_compact(self, ps: PathSet):
+        j = ps.jumps if len(ps.jumps) else np.zeros(1)
+        code = ps.row_code()
+        self._ck(self.lib.epv_upload_paths_compact(
+            self.h, ps.n_sites, ps.n_nodes, code.ctypes.data_as(L.u16p), _d(j), len(ps.jumps),
+            _d(ps.tot_time)))
+        self.n_sites = ps.n_sites
+
+    def download_paths_compact(self, node_names=()) -> PathSet:
+        n_sites, n_nodes, n_jumps = self.paths_size()
+        code = np.zeros(n_sites * n_nodes, np.uint16)
+        jumps = np.zeros(max(1, n_jumps))
+        tot = np.zeros(n_nodes)
+        n = C.c_uint64()
+        self._ck(self.lib.epv_download_paths_compact(
+            self.h, code.ctypes.data_as(L.u16p), _d(jumps), len(jumps), C.byref(n), _d(tot)))
+        return PathSet.from_row_code(n_sites, n_nodes, code, jumps[:n.value].copy(), tot,
+                                     list(node_names))
+
+    def upload_compact_raw(self, n_sites, n_nodes, code_ptr, jumps_ptr, n_jumps, tot_time):
+        tt = _f64(tot_time)
+        self._ck(self.lib.epv_upload_paths_compact(
+            self.h, n_sites, n_nodes, C.cast(code_ptr, L.u16p), C.cast(jumps_ptr, L.dp), n_jumps,
+            _d(tt)))
+        self.n_sites = n_sites
+
+    def download_compact_raw(self, code_ptr, jumps_ptr, jumps_cap) -> int:
+        tot = np.zeros(self.n_nodes)
+        n = C.c_uint64()
+        self._ck(self.lib.epv_download_paths_compact(
+            self.h, C.cast(code_ptr, L.u16p), C.cast(jumps_ptr, L.dp), jumps_cap, C.byref(n),
+            _d(tot)))
+        return n.value
+
     def jump_counts(self) -> np.ndarray:
         out = np.zeros(self.n_nodes, np.uint64)
         self._ck(self.lib.epv_jump_counts(self.h, _u64(out)))

@@ -59,6 +59,21 @@ class PathSet:
         """Jump count of every row, shape [n_nodes, n_sites]."""
         return np.diff(self.row_off).astype(np.int64).reshape(self.n_nodes, self.n_sites)
 
+    def row_code(self) -> np.ndarray:
+        """Compact per-row code of epv_upload_paths_compact: jump count | init_state << 15."""
+        n = np.diff(self.row_off)
+        if n.size and int(n.max()) > 0x7fff:
+            raise ValueError("a row holds more than 32767 jumps: use the CSR format")
+        return (n.astype(np.uint16) | (self.init_state.astype(np.uint16) << np.uint16(15)))
+
+    @classmethod
+    def from_row_code(cls, n_sites, n_nodes, code, jumps, tot_time, node_names=()):
+        code = np.asarray(code, dtype=np.uint16)
+        off = np.zeros(code.size + 1, np.uint64)
+        np.cumsum(code & np.uint16(0x7fff), dtype=np.uint64, out=off[1:])
+        return cls(n_sites, n_nodes, (code >> np.uint16(15)).astype(np.uint8), off, jumps, tot_time,
+                   list(node_names))
+
     def end_state(self) -> np.ndarray:
         """State at the end of every row (Path::end_state, Path.hpp:53-55)."""
         st = self.init_state.reshape(self.n_nodes, self.n_sites).astype(np.int64)

@@ -75,6 +75,17 @@ int epv_paths_size(epv_ctx *ctx, uint64_t *n_sites, uint64_t *n_nodes,
                    uint64_t *n_jumps);
 int epv_download_paths(epv_ctx *ctx, uint8_t *init_state, uint64_t *row_off,
                        double *jumps, double *tot_time);
+/* The same exchange at 2 bytes per row instead of 9 (the per-row arrays dominate the PCIe
+ * traffic: a row of Path.hpp:38-48 holds 0.1-2 jumps): row_code[node*n_sites + site] =
+ * number of jumps of the row | init_state << 15 (root rows: count 0); jumps as above, in row
+ * order; n_jumps = their number (checked against the codes).  Offsets and state bit sets
+ * are built on the device.  A row with more than 32767 jumps needs the format above. */
+int epv_upload_paths_compact(epv_ctx *ctx, uint64_t n_sites, uint64_t n_nodes,
+                             const uint16_t *row_code, const double *jumps,
+                             uint64_t n_jumps, const double *tot_time);
+/* jumps holds room for jumps_cap values; *n_jumps receives the number needed/written. */
+int epv_download_paths_compact(epv_ctx *ctx, uint16_t *row_code, double *jumps,
+                               uint64_t jumps_cap, uint64_t *n_jumps, double *tot_time);
 
 /* ---- the sampler (SingleSiteSampler.hpp:35-81) --------------------------------- */
 /* replaces SingleSiteSampler::reset (SingleSiteSampler.cpp:449-475): caches the
