@@ -18,7 +18,9 @@ int read_branch_totals(epv_ctx *c, std::vector<uint64_t> &tot) {
                                 c->d_off[c->cur] + (uint64_t)bi*c->off_pitch + c->n_own(),
                                 sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
   EPV_CUDA(c, cudaStreamSynchronize(c->stream));
-  for (int bi = 0; bi < n_br; ++bi) tot[bi] = reinterpret_cast<uint32_t *>(c->h_mail)[bi];
+  uint64_t sum = 0;
+  for (int bi = 0; bi < n_br; ++bi) sum += tot[bi] = reinterpret_cast<uint32_t *>(c->h_mail)[bi];
+  c->jumps_per_row = (double)sum/((double)n_br*(double)c->n_own());
   return 0;
 }
 
@@ -155,6 +157,9 @@ static int ensure_shape(epv_ctx *c, uint64_t n_sites) {
 // Jump buffers (+ the proposal staging blob): reallocated only when a branch no longer fits.
 static int ensure_jumps(epv_ctx *c, const std::vector<uint64_t> &count) {
   const int n_br = c->n_nodes - 1;
+  uint64_t sum = 0;
+  for (int bi = 0; bi < n_br; ++bi) sum += count[bi];
+  c->jumps_per_row = (double)sum/((double)n_br*(double)c->n_own());
   bool fits = (int)c->h_jcap.size() == n_br && c->d_jmp[0];
   for (int bi = 0; fits && bi < n_br; ++bi) fits = 4*count[bi] <= 3*c->h_jcap[bi];
   for (int bi = 0; bi < n_br; ++bi)

@@ -46,6 +46,7 @@ struct epv_ctx {
   // colour-pass machinery
   unsigned long long *d_desc = nullptr;
   uint32_t n_tiles = 0, epoch = 0, ticket_base = 0;
+  double jumps_per_row = 0.0;                // owned rows, refreshed whenever the totals are read
   uint32_t *d_ticket = nullptr, *d_scratch_ctr = nullptr;
   double *d_scratch = nullptr;
   uint32_t scratch_slots = 2048, scratch_cap = 2048;

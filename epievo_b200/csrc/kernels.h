@@ -24,6 +24,7 @@ struct PassArgs {
   int64_t global0;            // global index of local site 0
   uint64_t n_global;
   int colour;
+  int coop;                   // warp-cooperative jump-time sampling (pays when jumps are sparse)
   uint64_t seed;
   uint32_t sweep;
   // single-pass chained scan (decoupled look-back) state

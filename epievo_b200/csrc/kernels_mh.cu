@@ -29,15 +29,20 @@ constexpr uint32_t STG_REJECTED = 0xffffffffu, STG_EMPTY = 0xfffffffeu;
 
 __device__ __forceinline__ int stage_header_words(int n_br) { return (n_br + 3) >> 2; }
 
-#ifndef EPV_MH_MINBLOCKS
-#define EPV_MH_MINBLOCKS 4      // <= 128 registers; measured best of 3/4/5 (5.5 / 6.2 / 6.5 ms)
+// CTAs per SM the update kernel is compiled for (register budget 65536 / (128 x this)).
+// Measured ms per pass at 3 / 4 / 5: 8-leaf tree (MAXN 16) 6.1 / 5.5 / 6.5; 4-branch test tree
+// (MAXN 8) 6.5 / 6.5 / 7.4; 32-leaf tree (MAXN 64) 7.7 / 8.9 / 10.6.
+#ifdef EPV_MH_MINBLOCKS
+__host__ __device__ constexpr int mh_minblocks(int) { return EPV_MH_MINBLOCKS; }
+#else
+__host__ __device__ constexpr int mh_minblocks(int maxn) { return maxn <= 16 ? 4 : 3; }
 #endif
 
 // jump-queue slots per thread (shared memory: 24 B each)
 __host__ __device__ constexpr int mh_qcap(int maxn) { return maxn <= 16 ? 8 : maxn <= 64 ? 16 : 24; }
 
 template <int MAXN, int MAXJ, bool HALO>
-__global__ void __launch_bounds__(MH_THREADS, EPV_MH_MINBLOCKS)
+__global__ void __launch_bounds__(MH_THREADS, mh_minblocks(MAXN))
 mh_update_kernel(const PassArgs a) {
   __shared__ ModelParams s_mp;
   __shared__ CtxTables s_tb;
@@ -64,7 +69,7 @@ mh_update_kernel(const PassArgs a) {
   {
     const bool active = st >= a.upd_lo && st < a.upd_hi && gsite >= 1 && gsite + 1 < (int64_t)a.n_global;
     SiteCtx c; c.pv = a.in; c.state = a.state; c.W = a.W; c.tree = a.tree; c.site = st;
-    int r = mh_site_flat<MAXN, PB, QCAP, HALO>(active, s_mp, s_tb, c, a.state, a.tri_llh, a.seed, a.sweep,
+    int r = mh_site_flat<MAXN, PB, QCAP, HALO>(active, a.coop != 0, s_mp, s_tb, c, a.state, a.tri_llh, a.seed, a.sweep,
                                          (uint64_t)gsite, a.n_global, S, pr, total);
     // -3: interval stack too small -- a property of the neighbours' rows only, so switching
     // to the generic per-branch routine here is unbiased (rare; runs divergently)
@@ -83,7 +88,7 @@ mh_update_kernel(const PassArgs a) {
         else { pr.pj = a.scratch + (uint64_t)slot*a.scratch_cap; pr.cap = (int)a.scratch_cap; }
       }
       const bool redo = again && r == -1;
-      const int r2 = mh_site_flat<MAXN, PB, QCAP, HALO>(redo && !generic, s_mp, s_tb, c, a.state, a.tri_llh,
+      const int r2 = mh_site_flat<MAXN, PB, QCAP, HALO>(redo && !generic, a.coop != 0, s_mp, s_tb, c, a.state, a.tri_llh,
                                                   a.seed, a.sweep, (uint64_t)gsite, a.n_global, S, pr, total);
       if (redo && !generic) r = r2;
       if (redo && generic)

@@ -209,7 +209,7 @@ coop_sample(const ModelParams &mp, QSlot *queue, int *excl, int qn, uint64_t see
 // of the function (measured: 2-4 active lanes per instruction).
 template <int MAXN, int PB, int QCAP, bool HALO>
 __device__ __forceinline__ int
-mh_site_flat(bool active, const ModelParams &mp, const CtxTables &tb, const SiteCtx &c,
+mh_site_flat(bool active, bool coop, const ModelParams &mp, const CtxTables &tb, const SiteCtx &c,
              uint8_t *state_rw, double *tri_llh, uint64_t seed, uint32_t sweep, uint64_t gsite,
              uint64_t n_global, FlatScratch<MAXN, PB, QCAP> &S, Proposal &pr, int &total_out) {
   constexpr unsigned FULL = 0xffffffffu;
@@ -309,7 +309,8 @@ mh_site_flat(bool active, const ModelParams &mp, const CtxTables &tb, const Site
   }
   // ---- 3. jump times of the queued intervals ---------------------------------------
   if (status <= 0) qn = 0;
-  coop_sample<QCAP>(mp, S.queue, S.excl, qn, seed, sweep, gsite);
+  // (warp-uniform switch; without it every owner samples its own queue: same streams, same result)
+  if (coop) coop_sample<QCAP>(mp, S.queue, S.excl, qn, seed, sweep, gsite);
   if (status > 0) {
     total = collect_queue(mp, S.queue, qn, seed, sweep, gsite, pr, total);
     if (total < 0) status = total;
