@@ -292,8 +292,16 @@ mh_site_flat(bool active, bool coop, const ModelParams &mp, const CtxTables &tb,
       bool need_jumps = e != prev;
       if (!need_jumps) {
         // P(no jump | start == end) = exp(-r_prev len) / P(prev -> prev)
-        const double ea = exp(-len*(prev ? mp.rate[ctx | 2] : mp.rate[ctx]));
-        need_jumps = !(u_jump*(prev ? P11 : P00) < ea);
+        // compare u P(prev -> prev) with exp(-x), x = r_prev len, through the alternating-series
+        // bounds 1 - x + x^2/2 - x^3/6 <= exp(-x) <= ... + x^4/24; exp itself only in the gap
+        // (the decision is the one exp would give: the margin covers the rounding of the bounds)
+        const double x = len*(prev ? mp.rate[ctx | 2] : mp.rate[ctx]);
+        const double lhs = u_jump*(prev ? P11 : P00);
+        const double lo = 1.0 + x*(-1.0 + x*(0.5 - x*(1.0/6.0)));
+        const double x2 = x*x;
+        if (lhs < lo - 1e-15) need_jumps = false;
+        else if (lhs > lo + x2*x2*(1.0/24.0) + 1e-15) need_jumps = true;
+        else need_jumps = !(lhs < exp(-x));
       }
       if (need_jumps) {
         if (qn == QCAP) total = collect_queue(mp, S.queue, qn, seed, sweep, gsite, pr, total);
