@@ -59,6 +59,12 @@ SIGNATURES = {
     "epv_estimate_rates": (C.c_double, [u64, dp, dp, C.c_double, dp, dp, dp]),
     "epv_estimate_rates_and_branches": (C.c_double, [u64, dp, dp, C.c_double, dp, dp, dp, dp]),
     "epv_set_one_change": (None, [dp, u64, dp]),
+    "epv_pathfile_read": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(C.c_void_p), u64p, u64p, u64p]),
+    "epv_pathfile_get": (C.c_int, [C.c_void_p, u8p, u64p, dp, dp]),
+    "epv_pathfile_node_name": (C.c_char_p, [C.c_void_p, u64]),
+    "epv_pathfile_free": (None, [C.c_void_p]),
+    "epv_pathfile_write": (C.c_int, [C.c_char_p, u64, u64, C.POINTER(C.c_char_p), u8p, u64p, dp, dp, C.c_int]),
+    "epv_io_last_error": (C.c_char_p, []),
     "epv_launch_count": (u64, [ctx_p]),
     "epv_mh_kernel_time": (C.c_int, [ctx_p, C.c_int, dp, u64p]),
     "epv_rebuild_kernel_time": (C.c_int, [ctx_p, dp]),

@@ -182,6 +182,47 @@ def read_paths(path_file: str) -> PathSet:
     return PathSet.from_rows(n_sites, n_nodes, init, rows, tot, names)
 
 
+def read_paths_native(path_file: str, n_threads: int = 0) -> PathSet:
+    """read_paths through the library's multi-threaded parser (epv_pathfile_read)."""
+    import ctypes as C
+
+    from . import _lib as L
+    lib = L.load()
+    h = C.c_void_p()
+    ns, nn, nj = C.c_uint64(), C.c_uint64(), C.c_uint64()
+    if lib.epv_pathfile_read(path_file.encode(), n_threads, C.byref(h), C.byref(ns), C.byref(nn), C.byref(nj)):
+        raise RuntimeError(lib.epv_io_last_error().decode())
+    try:
+        n_rows = ns.value * nn.value
+        init = np.zeros(n_rows, np.uint8)
+        off = np.zeros(n_rows + 1, np.uint64)
+        jumps = np.zeros(max(1, nj.value))
+        tot = np.zeros(nn.value)
+        if lib.epv_pathfile_get(h, init.ctypes.data_as(L.u8p), off.ctypes.data_as(L.u64p),
+                                jumps.ctypes.data_as(L.dp), tot.ctypes.data_as(L.dp)):
+            raise RuntimeError(lib.epv_io_last_error().decode())
+        names = [lib.epv_pathfile_node_name(h, b).decode() for b in range(nn.value)]
+    finally:
+        lib.epv_pathfile_free(h)
+    return PathSet(ns.value, nn.value, init, off, jumps[:nj.value].copy(), tot, names)
+
+
+def write_paths_native(path_file: str, ps: PathSet, node_names: Sequence[str] = (),
+                       n_threads: int = 0) -> None:
+    """write_paths through the library's multi-threaded formatter (epv_pathfile_write)."""
+    import ctypes as C
+
+    from . import _lib as L
+    lib = L.load()
+    names = list(node_names) or list(ps.node_names) or ["node_%d" % i for i in range(ps.n_nodes)]
+    arr = (C.c_char_p * ps.n_nodes)(*[n.encode() for n in names])
+    j = ps.jumps if len(ps.jumps) else np.zeros(1)
+    if lib.epv_pathfile_write(path_file.encode(), ps.n_sites, ps.n_nodes, arr,
+                              ps.init_state.ctypes.data_as(L.u8p), ps.row_off.ctypes.data_as(L.u64p),
+                              j.ctypes.data_as(L.dp), ps.tot_time.ctypes.data_as(L.dp), n_threads):
+        raise RuntimeError(lib.epv_io_last_error().decode())
+
+
 def _fmt(x: float) -> str:
     # operator<<(ostream, Path) sets precision(max_digits10) = 17 significant digits in
     # the default (%g-like) float format (Path.cpp:62-71).

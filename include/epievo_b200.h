@@ -196,6 +196,28 @@ double epv_estimate_rates_and_branches(uint64_t n_nodes, const double *J,
 /* replaces set_one_change_per_site_per_unit_time (:318-334). */
 void epv_set_one_change(double *rates, uint64_t n_nodes, double *branches);
 
+/* ---- local-paths text files (host only, multi-threaded) ------------- */
+/* replaces read_paths (Path.cpp:123-148): parses the file with n_threads threads
+ * (<= 0: all cores) into an opaque handle and reports the sizes; epv_pathfile_get fills
+ * caller-allocated arrays in the epv_upload_paths exchange format (root rows empty);
+ * node names as in the file.  Errors: non-zero + epv_io_last_error() (thread-local),
+ * "cannot read: <file>" as the reference throws. */
+typedef struct epv_pathfile epv_pathfile;
+int epv_pathfile_read(const char *filename, int n_threads, epv_pathfile **out,
+                      uint64_t *n_sites, uint64_t *n_nodes, uint64_t *n_jumps);
+int epv_pathfile_get(const epv_pathfile *f, uint8_t *init_state, uint64_t *row_off,
+                     double *jumps, double *tot_time);
+const char *epv_pathfile_node_name(const epv_pathfile *f, uint64_t node);
+void epv_pathfile_free(epv_pathfile *f);
+/* replaces write_root_to_pathfile_local + append_to_pathfile_local
+ * (prog/epievo_est_params_histories.cpp:56-75) with operator<<(ostream, Path)
+ * (Path.cpp:62-71): byte-identical output, formatted by n_threads threads. */
+int epv_pathfile_write(const char *filename, uint64_t n_sites, uint64_t n_nodes,
+                       const char *const *node_names, const uint8_t *init_state,
+                       const uint64_t *row_off, const double *jumps,
+                       const double *tot_time, int n_threads);
+const char *epv_io_last_error(void);
+
 /* ---- instrumentation ------------------------------------------------------------- */
 /* Kernel launches issued by this context since creation (bench "gpu_launches"). */
 uint64_t epv_launch_count(const epv_ctx *ctx);

@@ -173,6 +173,47 @@ ref_store_paths(uint8_t *init_state, uint64_t *row_off, double *jumps,
   row_off[n_nodes*n_sites] = off;
 }
 
+/* ---- local-paths files: the reference's reader / writer ------- */
+/* read_paths (Path.cpp:123-148) + the transposition every caller does
+ * (prog/epievo_est_params_histories.cpp:183-192).  Returns seconds spent in read_paths,
+ * < 0 on failure. */
+double
+ref_read_paths_file(const char *filename, uint64_t *n_sites, uint64_t *n_nodes) {
+  vector<string> names;
+  vector<vector<Path> > orig;
+  const auto t0 = std::chrono::steady_clock::now();
+  try { read_paths(filename, names, orig); }
+  catch (const std::exception &) { return -1.0; }
+  const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  if (orig.size() < 2) return -1.0;
+  const size_t ns = orig[1].size(), nn = orig.size();
+  g_paths.assign(ns, vector<Path>(nn));
+  for (size_t i = 0; i < ns; ++i)
+    for (size_t b = 1; b < nn; ++b) g_paths[i][b] = orig[b][i];
+  *n_sites = ns; *n_nodes = nn;
+  return sec;
+}
+
+/* The writer of prog/epievo_est_params_histories.cpp:56-75 (static there): the same
+ * statements over operator<<(ostream, Path) (Path.cpp:62-71).  Returns seconds. */
+double
+ref_write_paths_file(const char *filename, uint64_t n_nodes, const char *const *names) {
+  const auto t0 = std::chrono::steady_clock::now();
+  {
+    std::ofstream out(filename);
+    if (!out) return -1.0;
+    out << "NODE:" << names[0] << std::endl;
+  }
+  for (size_t b = 1; b < n_nodes; ++b) {
+    std::ofstream out(filename, std::ofstream::app);
+    if (!out) return -1.0;
+    out << "NODE:" << names[b] << std::endl;
+    for (size_t i = 0; i < g_paths.size(); ++i)
+      out << i << '\t' << g_paths[i][b] << '\n';
+  }
+  return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+
 /* ---- a13: whole-data per-branch J/D --------------------------------------- */
 void
 ref_get_suff_stats(double *J, double *D) {

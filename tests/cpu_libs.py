@@ -80,6 +80,9 @@ class CpuLib:
           [C.c_uint64, _dp, _dp, C.c_double, _dp, _dp, _dp, _dp])
         f("set_one_change", None, [_dp, C.c_uint64, _dp])
         f("scale_jump_times", None, [C.c_uint64, _dp])
+        if prefix == "ref_":
+            f("read_paths_file", C.c_double, [C.c_char_p, _u64p, _u64p])
+            f("write_paths_file", C.c_double, [C.c_char_p, C.c_uint64, C.POINTER(C.c_char_p)])
         if prefix == "orc_":
             f("log_likelihood", C.c_double, [_dp, _dp, _dp])
             f("gradient", None, [_dp] * 4)
@@ -145,6 +148,24 @@ class CpuLib:
         self._store_paths(_u8(init), _u64(off), _d(jumps), _d(tot))
         return PathSet(self._n_sites, self._n_nodes, init, off,
                        jumps[:int(off[-1])].copy(), tot)
+
+    def read_paths_file(self, filename: str, timing: bool = False):
+        """The reference's read_paths on a local-paths file (reference build only)."""
+        ns, nn = np.zeros(1, np.uint64), np.zeros(1, np.uint64)
+        sec = self._read_paths_file(filename.encode(), _u64(ns), _u64(nn))
+        if sec < 0:
+            raise RuntimeError("cannot read: " + filename)
+        self._n_sites, self._n_nodes = int(ns[0]), int(nn[0])
+        ps = self.store_paths()
+        return (ps, sec) if timing else ps
+
+    def write_paths_file(self, filename: str, names) -> float:
+        """The reference's writer statements on the loaded paths; returns seconds."""
+        arr = (C.c_char_p * len(names))(*[n.encode() for n in names])
+        sec = self._write_paths_file(filename.encode(), len(names), arr)
+        if sec < 0:
+            raise RuntimeError("bad output file: " + filename)
+        return sec
 
     def get_suff_stats(self) -> Tuple[np.ndarray, np.ndarray]:
         J = np.zeros(self._n_nodes * 8)
