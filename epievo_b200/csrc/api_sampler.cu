@@ -80,7 +80,7 @@ int one_pass(epv_ctx *c, int colour, uint64_t seed, uint32_t sweep) {
     if (c->ev_pending == epv_ctx::EV_RING) drain_timing(c);
     cudaEventRecord(c->ev_ring[3*c->ev_pending], c->stream);
   }
-  launch_mh_pass(a, c->stream);
+  const int n_upd = launch_mh_pass(a, c->stream);   // 1, or 2 for a sharded context
   if (c->timing) {
     cudaEventRecord(c->ev_ring[3*c->ev_pending + 1], c->stream);
   }
@@ -89,7 +89,7 @@ int one_pass(epv_ctx *c, int colour, uint64_t seed, uint32_t sweep) {
     cudaEventRecord(c->ev_ring[3*c->ev_pending + 2], c->stream);
     ++c->ev_pending;
   }
-  c->launches += 2; ++c->mh_launches;
+  c->launches += n_upd + 1; ++c->mh_launches;
   c->ticket_base += c->n_tiles;
   c->cur ^= 1;
   c->stats_valid = false;

@@ -39,6 +39,8 @@ struct PassArgs {
   uint32_t scratch_slots, scratch_cap;
   // staging of the accepted proposals' rows between the update and the rebuild kernel
   uint64_t n_groups;          // groups of 3 sites covering the local sites
+  // groups one launch works on: index i < g_count maps to group g_first + i (+ g_skip when i >= g_split)
+  uint64_t g_first, g_split, g_skip, g_count;
   uint32_t *stage_off;        // [n_groups] offset into stage, or rejected / empty marker
   double *stage;              // blobs: ceil(n_br/4) words of u16 jump counts + jump times
   unsigned long long *stage_ctr;
@@ -47,7 +49,7 @@ struct PassArgs {
   unsigned long long *n_accept;
 };
 
-void launch_mh_pass(const PassArgs &a, cudaStream_t st);       // update kernel
+int launch_mh_pass(const PassArgs &a, cudaStream_t st);       // update kernel
 void launch_csr_rebuild(const PassArgs &a, cudaStream_t st);   // re-compaction kernel
 size_t mh_pass_smem_bytes(int n_nodes);
 

@@ -1,14 +1,9 @@
 mkdir -p gpurun_out
-python -m pytest tests -m gpu -q > gpurun_out/pytest_gpu.log 2>&1; tail -3 gpurun_out/pytest_gpu.log
-for w in bal8 testtree pairwise bal32; do
-  python bench.py --workload $w --steps 3 --warmup 3 > gpurun_out/bench_$w.json 2> gpurun_out/bench_$w.err || tail -3 gpurun_out/bench_$w.err
-  python - <<PY
+python -m pytest tests/test_gpu_sharded.py tests/test_gpu_compact.py tests/test_gpu_sampler.py -m gpu -q -x > gpurun_out/pytest_gpu.log 2>&1; tail -3 gpurun_out/pytest_gpu.log
+python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 3 --warmup 3 > gpurun_out/bench_n2.json 2> gpurun_out/bench_n2.err || tail -5 gpurun_out/bench_n2.err
+python - <<PY
 import json
-d=json.loads(open('gpurun_out/bench_$w.json').read().strip().splitlines()[-1])
-print('$w', '%.3e'%d['value'], 'e2e %.3e'%d['e2e']['value'], 'upd_ms=%.3f'%d['roofline']['avg_launch_ms'], 'rb_ms=%.3f'%d['roofline']['rebuild_kernel_avg_ms'], 'frac=%.4f'%d['roofline']['frac'], 'cpu %.3e'%d['cpu_baseline']['value'])
+d=json.loads(open('gpurun_out/bench_n2.json').read().strip().splitlines()[-1])
+print('N=2', '%.4e'%d['value'], 'e2e %.4e'%d['e2e']['value'], 'ms/step %.1f'%d['ms_per_step'], 'upd_ms=%.3f'%d['roofline']['avg_launch_ms'])
 PY
-done
-python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; cat gpurun_out/bench_ref.json | cut -c1-600
-B="python bench.py --steps 1 --warmup 1 --burn-in 2 --batch 2 --no-cpu-baseline"
-$B > gpurun_out/plain_l.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_v5.csv $B > gpurun_out/ncu_l.log 2>&1
-tail -1 gpurun_out/ncu_l.log | cut -c1-200
+python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29512 tools/dist_check.py > gpurun_out/dist_check_n2.txt 2>&1; tail -3 gpurun_out/dist_check_n2.txt
