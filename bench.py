@@ -161,6 +161,7 @@ def main():
     ap.add_argument("--cpu-procs", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-mcem", action="store_true")
     ap.add_argument("--exchange", choices=("compact", "csr"), default="compact",
                     help="host exchange format of the e2e leg (u16 row codes, or 9-byte CSR rows)")
     args = ap.parse_args()
@@ -365,6 +366,30 @@ def main():
                  "frac_of_hbm_peak": ss_bytes / (ss_ms * 1e-3) / 1e9 / peak,
                  "rows_per_s": n_own * n_br / (ss_ms * 1e-3)}
 
+    # ---- one whole MCEM iteration, paths resident (reset + E-step + M-step + rescale) ------
+    # prog/epievo_est_params_histories.cpp:239-264; N=1: epv_mcem_iteration, N>1: the same
+    # steps with the halo exchange and one all-reduce (sharded.mcem_iteration).  Wall clock
+    # between device synchronisations (the M-step runs on the host), max over ranks.
+    def mcem_once(first_sweep):
+        if world == 1:
+            return ctx.mcem_iteration(args.burn_in, args.batch, 2024, first_sweep, rates, T, tree.branches)
+        return S.mcem_iteration([shard], transport, args.burn_in, args.batch, 2024, first_sweep, rates, T,
+                                tree.branches, allreduce=transport.allreduce_sum)
+    mcem = None
+    if not args.no_mcem:
+        barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        out = mcem_once(sweep_no)
+        torch.cuda.synchronize()
+        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        sweep_no += sweeps
+        mcem = {"ms": float(dt.item()) * 1e3, "burn_in": args.burn_in, "batch": args.batch,
+                "sites": int(n_global), "acc_rate": float(out[4]),
+                "what": "set_model + reset + run_mcmc(L,B) + M-step (estimate_rates, host) + scale_jump_times"}
+
     # ---- CPU baseline (rank 0, N=1 only) ---------------------------------------------------
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -376,6 +401,9 @@ def main():
                         "sample": "%d sites of the same workload, one run_mcmc(L=%d,B=%d), single "
                                   "thread (the reference is single-threaded), %.1f s" % (n_s, bi, ba, per_step[0])}
 
+    if mcem and cpu_baseline:
+        mcem["cpu_reference_est_s"] = (n_global - 2) * n_br * sweeps / cpu_baseline["value"]
+        mcem["cpu_note"] = "reference on 1 core, extrapolated from the cpu_baseline sample (its cost is linear in sites)"
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -383,7 +411,7 @@ def main():
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": workload_config(args, n_br), "clocks": clk, "e2e": e2e,
             "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu_baseline,
-            "acc_rate": acc, "suffstats_pass": suffstats,
+            "acc_rate": acc, "suffstats_pass": suffstats, "mcem_iter": mcem,
         }
         print(json.dumps(line))
     ctx.close()

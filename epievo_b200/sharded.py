@@ -144,6 +144,41 @@ def run_mcmc(shards: Sequence[Shard], transport, burn_in: int, batch: int, seed:
             flat[-1] / (batch * (n_global - 2)))
 
 
+def mcem_iteration(shards: Sequence[Shard], transport, burn_in: int, batch: int, seed: int,
+                   first_sweep: int, rates, T, branches, optimize_branches: bool = False,
+                   param_tol: float = 1e-10, allreduce=None):
+    """One MCEM iteration over shards -- the body of the loop at
+    prog/epievo_est_params_histories.cpp:239-264, i.e. what epv_mcem_iteration does on one
+    GPU: new model -> reset -> E-step (run_mcmc, J/D all-reduced) -> M-step on the host
+    (identical on every rank) -> scale_jump_times.  Returns (rates, T, branches, baseline,
+    acc_rate, llh)."""
+    import ctypes as C
+
+    from . import _lib as L
+    lib = L.load()
+    r = np.ascontiguousarray(rates, np.float64).copy()
+    t = np.ascontiguousarray(T, np.float64).copy()
+    br = np.ascontiguousarray(branches, np.float64).copy()
+    bl = np.zeros(4)
+    for s in shards:
+        s.ctx.set_model(r, t)
+        s.ctx.reset()
+    J, D, acc = run_mcmc(shards, transport, burn_in, batch, seed, first_sweep, allreduce=allreduce)
+    Jf, Df = np.ascontiguousarray(J.reshape(-1)), np.ascontiguousarray(D.reshape(-1))
+    n_nodes = shards[0].ctx.n_nodes
+
+    def d(a):
+        return a.ctypes.data_as(L.dp)
+    if not optimize_branches:
+        llh = lib.epv_estimate_rates(n_nodes, d(Jf), d(Df), param_tol, d(r), d(t), d(bl))
+        lib.epv_set_one_change(d(r), n_nodes, d(br))
+    else:
+        llh = lib.epv_estimate_rates_and_branches(n_nodes, d(Jf), d(Df), param_tol, d(r), d(br), d(t), d(bl))
+    for s in shards:
+        s.ctx.scale_jump_times(br)
+    return r, t, br, bl, acc, llh
+
+
 def gather_paths(parts: Sequence[PathSet], n_global: int, world: int) -> PathSet:
     """Owned blocks of every shard's local PathSet (halo stripped) -> one PathSet."""
     n_nodes = parts[0].n_nodes

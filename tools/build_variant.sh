@@ -7,7 +7,7 @@ name=$1; shift
 mkdir -p variants/obj_$name
 FLAGS="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -Xcompiler -fno-fast-math --fmad=true"
 objs=""
-for f in csrc/*.cu csrc/host_model.cpp; do
+for f in csrc/*.cu csrc/*.cpp; do
   o=variants/obj_$name/$(basename ${f%.*}).o
   nvcc $FLAGS "$@" -c $f -o $o &
   objs="$objs $o"
