@@ -219,7 +219,6 @@ mh_site_flat(bool active, bool coop, const ModelParams &mp, const CtxTables &tb,
   int status = 1;                       // becomes <0 on failure; the lane then idles
   StateWin<(MAXN + 63)/64> sw;
   if (active) sw.load(c.state, c.W, s, c.pv.n_local);
-#ifdef EPV_PREFETCH
   // the three passes below walk the CSR offsets of sites s-2..s+3 on every branch: start the
   // loads of all those lines now (no registers held; the lanes of a warp share 3-4 lines per
   // branch) instead of missing on them one branch at a time on the warp's critical path
@@ -227,15 +226,10 @@ mh_site_flat(bool active, bool coop, const ModelParams &mp, const CtxTables &tb,
     const uint32_t *o = c.pv.off + (s - 2 - c.pv.own_lo);
     for (int bi = n_nodes - 2; bi >= 0; --bi) {
       const uint32_t *p = o + (uint64_t)bi*c.pv.off_pitch;
-#if EPV_PREFETCH == 1
       asm volatile("prefetch.global.L1 [%0];" :: "l"(p));
-#else
-      asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
-#endif
     }
     asm volatile("prefetch.global.L2 [%0];" :: "l"(tri_llh + s - 1));
   }
-#endif
 
   // ---- 1. upward pruning, flat over (branch, interval) ----------------------------
   for (int v = 0; v < n_nodes; ++v) { q[2*v] = 1.0; q[2*v + 1] = 1.0; pr.pn[v] = 0; }
