@@ -59,6 +59,12 @@ SIGNATURES = {
     "epv_estimate_rates": (C.c_double, [u64, dp, dp, C.c_double, dp, dp, dp]),
     "epv_estimate_rates_and_branches": (C.c_double, [u64, dp, dp, C.c_double, dp, dp, dp, dp]),
     "epv_set_one_change": (None, [dp, u64, dp]),
+    "epv_indep_suffstats": (C.c_int, [ctx_p, dp, dp]),
+    "epv_indep_expectation": (C.c_int, [ctx_p, dp, dp, dp]),
+    "epv_indep_update_paths": (C.c_int, [ctx_p, dp, u64, u64]),
+    "epv_indep_tables": (None, [C.c_double, C.c_double, C.c_double, dp, dp, dp, dp, dp]),
+    "epv_indep_estimate_rates": (None, [u64, dp, dp, dp]),
+    "epv_indep_estimate_rates_and_branches": (None, [u64, dp, dp, dp, dp]),
     "epv_pathfile_read": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(C.c_void_p), u64p, u64p, u64p]),
     "epv_pathfile_get": (C.c_int, [C.c_void_p, u8p, u64p, dp, dp]),
     "epv_pathfile_node_name": (C.c_char_p, [C.c_void_p, u64]),

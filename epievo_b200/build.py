@@ -13,7 +13,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libepievo_b200.so")
 OBJ = os.path.join(HERE, "build")
 
-CU_SOURCES = ["kernels_mh.cu", "kernels_aux.cu", "kernels_stats.cu", "kernels_halo.cu", "kernels_compact.cu",
+CU_SOURCES = ["kernels_mh.cu", "kernels_aux.cu", "kernels_stats.cu", "kernels_halo.cu", "kernels_compact.cu", "kernels_indep.cu",
               "api_core.cu", "api_paths.cu", "api_sampler.cu", "api_debug.cu", "api_halo.cu"]
 CXX_SOURCES = ["host_model.cpp", "paths_io.cpp"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

@@ -102,7 +102,7 @@ void epv_destroy(epv_ctx *c) {
   free_paths(c);
   cudaFree(c->d_parent); cudaFree(c->d_subtree); cudaFree(c->d_branch);
   cudaFree(c->d_err); cudaFree(c->d_nacc); cudaFree(c->d_ticket); cudaFree(c->d_scratch_ctr);
-  cudaFree(c->d_stg_ctr);
+  cudaFree(c->d_stg_ctr); cudaFree(c->d_itab); cudaFree(c->d_iacc);
   cudaFree(c->d_scratch); cudaFree(c->d_out9); cudaFree(c->d_mail); cudaFreeHost(c->h_mail);
   cudaFree(c->d_J); cudaFree(c->d_D); cudaFree(c->d_Jsum); cudaFree(c->d_Dsum); cudaFree(c->d_ss);
   cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1);

@@ -49,7 +49,9 @@ int do_reset(epv_ctx *c) {
   return 0;
 }
 
-int one_pass(epv_ctx *c, int colour, uint64_t seed, uint32_t sweep) {
+struct IndepLaunch { const IndepTab *tab; double r0, r1; };
+
+int one_pass(epv_ctx *c, int colour, uint64_t seed, uint32_t sweep, const IndepLaunch *indep = nullptr) {
   if (++c->epoch >= (1u << 30)) {
     EPV_CUDA(c, cudaMemsetAsync(c->d_desc, 0, (size_t)(c->n_nodes - 1)*c->n_tiles*sizeof(unsigned long long), c->stream));
     c->epoch = 1;
@@ -80,7 +82,9 @@ int one_pass(epv_ctx *c, int colour, uint64_t seed, uint32_t sweep) {
     if (c->ev_pending == epv_ctx::EV_RING) drain_timing(c);
     cudaEventRecord(c->ev_ring[3*c->ev_pending], c->stream);
   }
-  const int n_upd = launch_mh_pass(a, c->stream);   // 1, or 2 for a sharded context
+  int n_upd = 1;
+  if (indep) launch_indep_sample(a, indep->tab, indep->r0, indep->r1, c->stream);
+  else n_upd = launch_mh_pass(a, c->stream);        // 1, or 2 for a sharded context
   if (c->timing) {
     cudaEventRecord(c->ev_ring[3*c->ev_pending + 1], c->stream);
   }
@@ -89,7 +93,8 @@ int one_pass(epv_ctx *c, int colour, uint64_t seed, uint32_t sweep) {
     cudaEventRecord(c->ev_ring[3*c->ev_pending + 2], c->stream);
     ++c->ev_pending;
   }
-  c->launches += n_upd + 1; ++c->mh_launches;
+  c->launches += n_upd + 1;
+  if (!indep) ++c->mh_launches;
   c->ticket_base += c->n_tiles;
   c->cur ^= 1;
   c->stats_valid = false;
@@ -314,6 +319,81 @@ int epv_accept_count(epv_ctx *c, int reset, uint64_t *n_accepted) {
   if (int r = read_accepts(c, &n)) return r;
   if (n_accepted) *n_accepted = n;
   if (reset) EPV_CUDA(c, cudaMemsetAsync(c->d_nacc, 0, sizeof(unsigned long long), c->stream));
+  return 0;
+}
+
+}  // extern "C"
+
+// ---- site-independent E-step of epievo_initialization (IndepSite.cpp) -------------------
+namespace {
+
+int indep_ready(epv_ctx *c, const double *rates) {
+  if (!c) return 1;
+  if (!c->n_sites) return fail(c, "no paths loaded");
+  if (rates && !(rates[0] > 0.0 && rates[1] > 0.0)) return fail(c, "the two rates must be positive");
+  cudaSetDevice(c->device);
+  if (c->itab_nodes != c->n_nodes) {
+    cudaFree(c->d_itab); cudaFree(c->d_iacc); c->d_itab = nullptr; c->d_iacc = nullptr;
+    EPV_CUDA(c, cudaMalloc(&c->d_itab, (size_t)c->n_nodes*sizeof(IndepTab)));
+    EPV_CUDA(c, cudaMalloc(&c->d_iacc, (size_t)4*c->n_nodes*sizeof(double)));
+    c->itab_nodes = c->n_nodes;
+  }
+  return 0;
+}
+
+int indep_tables(epv_ctx *c, const double *rates) {
+  std::vector<IndepTab> tab(c->n_nodes);
+  std::memset(tab.data(), 0, tab.size()*sizeof(IndepTab));
+  for (int v = 1; v < c->n_nodes; ++v)
+    epv_indep_tables(rates[0], rates[1], c->h_branch[v], tab[v].P, tab[v].J0, tab[v].J1, tab[v].D0, tab[v].D1);
+  EPV_CUDA(c, cudaStreamSynchronize(c->stream));           // the previous table may still be in use
+  EPV_CUDA(c, cudaMemcpyAsync(c->d_itab, tab.data(), tab.size()*sizeof(IndepTab), cudaMemcpyHostToDevice, c->stream));
+  EPV_CUDA(c, cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int indep_read(epv_ctx *c, double *J, double *D) {
+  std::vector<double> acc((size_t)4*c->n_nodes);
+  EPV_CUDA(c, cudaMemcpyAsync(acc.data(), c->d_iacc, acc.size()*sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  EPV_CUDA(c, cudaStreamSynchronize(c->stream));
+  EPV_CUDA(c, cudaGetLastError());
+  for (int v = 0; v < c->n_nodes; ++v) {
+    J[2*v] = acc[4*v]; J[2*v + 1] = acc[4*v + 1];
+    D[2*v] = acc[4*v + 2]; D[2*v + 1] = acc[4*v + 3];
+  }
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int epv_indep_suffstats(epv_ctx *c, double *J, double *D) {
+  if (int r = indep_ready(c, nullptr)) return r;
+  launch_indep_stats(c->view(c->cur), c->d_state, c->W, c->tree(), c->d_iacc, c->sm_count, c->stream);
+  ++c->launches;
+  return indep_read(c, J, D);
+}
+
+int epv_indep_expectation(epv_ctx *c, const double *rates, double *J, double *D) {
+  if (int r = indep_ready(c, rates)) return r;
+  if (int r = indep_tables(c, rates)) return r;
+  const double pi0 = rates[1]/(rates[0] + rates[1]);       // root_post_prob0, IndepSite.cpp:94
+  launch_indep_expect(c->view(c->cur), c->d_state, c->W, c->tree(), c->d_itab, pi0, c->d_iacc, c->sm_count,
+                      c->stream);
+  ++c->launches;
+  return indep_read(c, J, D);
+}
+
+int epv_indep_update_paths(epv_ctx *c, const double *rates, uint64_t seed, uint64_t iteration) {
+  if (int r = indep_ready(c, rates)) return r;
+  if (int r = indep_tables(c, rates)) return r;
+  IndepLaunch il; il.tab = c->d_itab; il.r0 = rates[0]; il.r1 = rates[1];
+  for (int colour = 0; colour < 3; ++colour)
+    if (int r = one_pass(c, colour, seed, (uint32_t)iteration, &il)) return r;
+  c->tri_valid = false;
+  if (int r = housekeeping(c)) return r;
+  EPV_CUDA(c, cudaGetLastError());
   return 0;
 }
 

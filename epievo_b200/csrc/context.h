@@ -54,6 +54,9 @@ struct epv_ctx {
   unsigned long long *d_nacc = nullptr;
 
   // statistics
+  epv::IndepTab *d_itab = nullptr;           // site-independent model: per-node tables, [n_nodes*4] sums
+  double *d_iacc = nullptr;
+  int itab_nodes = 0;
   double *d_J = nullptr, *d_D = nullptr, *d_Jsum = nullptr, *d_Dsum = nullptr, *d_out9 = nullptr;
   unsigned long long *d_ss = nullptr;
   bool stats_valid = false;

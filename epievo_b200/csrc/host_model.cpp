@@ -3,6 +3,7 @@
 // on log-rates under the 5-free-parameter constraint, optional branch-length update).
 // Host code on purpose: the inputs are the 16*(n_nodes) J/D doubles the device
 // reduced; nothing here touches paths.
+#include <algorithm>
 #include <cfloat>
 #include <cmath>
 #include <cstring>
@@ -177,6 +178,70 @@ double epv_estimate_rates_and_branches(uint64_t n_nodes, const double *J, const 
   std::memcpy(rates, best, sizeof best);
   std::memcpy(branches, nb.data(), n_nodes*sizeof(double));
   return llh8(Jc, Dc, rates);
+}
+
+}  // extern "C"
+
+/* ---- site-independent 2-rate model of epievo_initialization (IndepSite.cpp) ------------ */
+extern "C" {
+
+/* Per-branch tables of the 2-state CTMC with rates (r0, r1) over time T: transition
+ * probabilities (continuous_time_trans_prob_mat, ContinuousTimeMarkovModel.cpp:142-161, which
+ * forms h as 1/exp(+x)) and the end-conditioned expectations of jump counts and holding times
+ * (expectation_J / expectation_D, :167-226).  2x2 matrices row-major over (start, end). */
+void epv_indep_tables(double r0, double r1, double T, double *P, double *J0, double *J1,
+                      double *D0, double *D1) {
+  const double s = r0 + r1, p = r0*r1;
+  {
+    const double h = 1.0/std::exp(T*s);
+    P[0] = (r0*h + r1)/s; P[1] = 1.0 - P[0];
+    P[3] = (r0 + r1*h)/s; P[2] = 1.0 - P[3];
+  }
+  const double e = std::exp(-s*T);
+  {
+    const double d = r1 - r0;
+    const double C1 = d*(1 - e)/s;
+    J0[0] = p*(T*(r1 - r0*e) - C1)/(s*(r1 + r0*e)); J1[0] = J0[0];
+    J0[3] = p*(T*(r0 - r1*e) + C1)/(s*(r0 + r1*e)); J1[3] = J0[3];
+    const double C2 = p*T*(1 + e)/(s*(1 - e));
+    const double C3 = (r0*r0 + r1*r1)/(s*s), C4 = (2*p)/(s*s);
+    J0[1] = C2 + C3; J1[1] = C2 - C4;
+    J0[2] = J1[1]; J1[2] = J0[1];
+  }
+  {
+    const double r00 = r0*r0, r11 = r1*r1;
+    const double C1 = 2*p*(1 - e)/s;
+    D0[0] = ((r11 + r00*e)*T + C1)/(s*(r1 + r0*e)); D1[0] = T - D0[0];
+    D1[3] = ((r00 + r11*e)*T + C1)/(s*(r0 + r1*e)); D0[3] = T - D1[3];
+    const double C2 = (p - r00)*(1 - e)/s;
+    D1[1] = ((r00 - p*e)*T + C2)/(s*(r0 - r0*e)); D0[1] = T - D1[1];
+    const double C3 = (p - r11)*(1 - e)/s;
+    D0[2] = ((r11 - p*e)*T + C3)/(s*(r1 - r1*e)); D1[2] = T - D0[2];
+  }
+}
+
+/* estimate_rates_indep (IndepSite.cpp:306-326): J, D are [n_nodes][2], entry 0 unused. */
+void epv_indep_estimate_rates(uint64_t n_nodes, const double *J, const double *D, double *rates) {
+  double Js[2] = {0.0, 0.0}, Ds[2] = {0.0, 0.0};
+  for (uint64_t b = 1; b < n_nodes; ++b) {
+    Js[0] += J[2*b]; Js[1] += J[2*b + 1];
+    Ds[0] += D[2*b]; Ds[1] += D[2*b + 1];
+  }
+  if (Ds[0] > 0) rates[0] = std::max(Js[0]/Ds[0], 10e-6);
+  if (Ds[1] > 0) rates[1] = std::max(Js[1]/Ds[1], 10e-6);
+}
+
+/* estimate_rates_and_branches_indep (:341-374) without its last loop: the caller rescales
+ * the stored paths with epv_scale_jump_times(ctx, branches). */
+void epv_indep_estimate_rates_and_branches(uint64_t n_nodes, const double *J, const double *D,
+                                           double *rates, double *branches) {
+  epv_indep_estimate_rates(n_nodes, J, D, rates);
+  for (uint64_t b = 1; b < n_nodes; ++b)
+    branches[b] *= (J[2*b] + J[2*b + 1])/(D[2*b]*rates[0] + D[2*b + 1]*rates[1]);
+  const double pi0 = rates[1]/(rates[0] + rates[1]), pi1 = rates[0]/(rates[0] + rates[1]);
+  const double scale = pi0*rates[0] + pi1*rates[1];                 /* indep_rate_scaling_factor */
+  for (uint64_t b = 0; b < n_nodes; ++b) branches[b] *= scale;
+  rates[0] /= scale; rates[1] /= scale;
 }
 
 }  // extern "C"

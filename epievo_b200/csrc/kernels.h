@@ -102,6 +102,14 @@ void launch_compact_import(const uint16_t *code, uint64_t n_sites, int n_nodes, 
 void launch_compact_export(const PathView &pv, const uint8_t *state, int W, uint64_t n_sites,
                            int n_nodes, uint16_t *code, unsigned *err, cudaStream_t st);
 
+// ---- site-independent E-step of epievo_initialization (kernels_indep.cu) -----------------
+struct IndepTab { double P[4], J0[4], J1[4], D0[4], D1[4]; };   // per node: 2x2 matrices, row-major (start, end)
+void launch_indep_expect(const PathView &pv, const uint8_t *state, int W, const TreeDev &tree,
+                         const IndepTab *tab, double pi0, double *acc, int sm_count, cudaStream_t st);
+void launch_indep_stats(const PathView &pv, const uint8_t *state, int W, const TreeDev &tree, double *acc,
+                        int sm_count, cudaStream_t st);
+void launch_indep_sample(const PassArgs &a, const IndepTab *tab, double r0, double r1, cudaStream_t st);
+
 // ---- halo exchange (multi-GPU): one boundary site per side per colour pass -------------
 // Record (8-byte words): [0..2] tri_llh[s-1], [s], [s+1]; [3] global site index;
 // [4 .. 4+SW) state bytes; then n_br u16 jump counts packed in CW words; then

@@ -221,6 +221,21 @@ class Context:
     def scale_jump_times(self, new_branches):
         self._ck(self.lib.epv_scale_jump_times(self.h, _d(_f64(new_branches))))
 
+    # -- site-independent E-step (epievo_initialization) ---------------------------------
+    def indep_suffstats(self):
+        """Sums over owned sites of the per-state J, D of every branch, [n_nodes, 2]."""
+        J, D = np.zeros(self.n_nodes * 2), np.zeros(self.n_nodes * 2)
+        self._ck(self.lib.epv_indep_suffstats(self.h, _d(J), _d(D)))
+        return J.reshape(-1, 2), D.reshape(-1, 2)
+
+    def indep_expectation(self, rates2):
+        J, D = np.zeros(self.n_nodes * 2), np.zeros(self.n_nodes * 2)
+        self._ck(self.lib.epv_indep_expectation(self.h, _d(_f64(rates2)), _d(J), _d(D)))
+        return J.reshape(-1, 2), D.reshape(-1, 2)
+
+    def indep_update_paths(self, rates2, seed: int, iteration: int = 0):
+        self._ck(self.lib.epv_indep_update_paths(self.h, _d(_f64(rates2)), seed, iteration))
+
     # -- parity probes ----------------------------------------------------------------
     def site_debug(self, site: int, cap: int = 4096):
         nn = self.n_nodes

@@ -196,6 +196,34 @@ double epv_estimate_rates_and_branches(uint64_t n_nodes, const double *J,
 /* replaces set_one_change_per_site_per_unit_time (:318-334). */
 void epv_set_one_change(double *rates, uint64_t n_nodes, double *branches);
 
+/* ---- site-independent E-step of epievo_initialization -------------- */
+/* Every site evolves as one 2-state CTMC with rates[2] = (0->1, 1->0) on every branch
+ * (IndepSite.cpp).  J and D are [n_nodes][2] (per start state; node 0 unused) and hold SUMS
+ * over the context's owned sites: compute_sufficient_statistics divides them by n_sites
+ * (IndepSite.cpp:296-301), expectation_sufficient_statistics does not (:228-238).
+ * A sharded context works on its owned sites; after epv_indep_update_paths refresh the
+ * halos (epv_halo_pack / unpack for colours 0, 1, 2) before the next MH pass. */
+/* replaces compute_sufficient_statistics (IndepSite.cpp:266-303), as sums. */
+int epv_indep_suffstats(epv_ctx *ctx, double *J, double *D);
+/* replaces expectation_sufficient_statistics (IndepSite.cpp:221-239). */
+int epv_indep_expectation(epv_ctx *ctx, const double *rates, double *J, double *D);
+/* replaces update_paths_indep (IndepSite.cpp:243-260): every owned site gets a new history
+ * given its leaf states and root state; Philox streams keyed (seed; iteration, site, node). */
+int epv_indep_update_paths(epv_ctx *ctx, const double *rates, uint64_t seed,
+                           uint64_t iteration);
+/* host: per-branch tables (continuous_time_trans_prob_mat, expectation_J, expectation_D,
+ * ContinuousTimeMarkovModel.cpp:142-226), 2x2 row-major over (start, end). */
+void epv_indep_tables(double r0, double r1, double T, double *P, double *J0, double *J1,
+                      double *D0, double *D1);
+/* host: estimate_rates_indep (IndepSite.cpp:306-326). */
+void epv_indep_estimate_rates(uint64_t n_nodes, const double *J, const double *D,
+                              double *rates);
+/* host: estimate_rates_and_branches_indep (:341-374) up to the path rescaling, which is
+ * epv_scale_jump_times(ctx, branches). */
+void epv_indep_estimate_rates_and_branches(uint64_t n_nodes, const double *J,
+                                           const double *D, double *rates,
+                                           double *branches);
+
 /* ---- local-paths text files (host only, multi-threaded) ------------- */
 /* replaces read_paths (Path.cpp:123-148): parses the file with n_threads threads
  * (<= 0: all cores) into an opaque handle and reports the sizes; epv_pathfile_get fills

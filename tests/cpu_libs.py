@@ -81,6 +81,13 @@ class CpuLib:
         f("set_one_change", None, [_dp, C.c_uint64, _dp])
         f("scale_jump_times", None, [C.c_uint64, _dp])
         if prefix == "ref_":
+            f("indep_load", None, [C.c_uint64, C.c_uint64, _u8p, _u64p, _dp, _dp])
+            f("indep_total_jumps", C.c_uint64, [])
+            f("indep_store", None, [_u8p, _u64p, _dp, _dp])
+            f("indep_suffstats", None, [C.c_uint64, _dp, _dp])
+            f("indep_expectation", None, [C.c_uint64, _u64p, _u64p, _dp, _dp, _dp, _dp])
+            f("indep_update_paths", None, [C.c_uint64, _u64p, _u64p, _dp, _dp, C.c_uint64])
+            f("indep_estimate", None, [C.c_uint64, _u64p, _u64p, _dp, _dp, _dp, _dp, C.c_int])
             f("read_paths_file", C.c_double, [C.c_char_p, _u64p, _u64p])
             f("write_paths_file", C.c_double, [C.c_char_p, C.c_uint64, C.POINTER(C.c_char_p)])
         if prefix == "orc_":
@@ -148,6 +155,44 @@ class CpuLib:
         self._store_paths(_u8(init), _u64(off), _d(jumps), _d(tot))
         return PathSet(self._n_sites, self._n_nodes, init, off,
                        jumps[:int(off[-1])].copy(), tot)
+
+    # -- IndepSite.cpp through the reference build -------------------------------------------
+    def indep_load(self, ps: PathSet) -> None:
+        self._i_sites, self._i_nodes = ps.n_sites, ps.n_nodes
+        self._indep_load(ps.n_sites, ps.n_nodes, _u8(ps.init_state), _u64(ps.row_off),
+                         _d(ps.jumps if len(ps.jumps) else np.zeros(1)), _d(ps.tot_time))
+
+    def indep_store(self) -> PathSet:
+        n_rows = self._i_sites * self._i_nodes
+        init, off = np.zeros(n_rows, np.uint8), np.zeros(n_rows + 1, np.uint64)
+        jumps, tot = np.zeros(max(1, int(self._indep_total_jumps()))), np.zeros(self._i_nodes)
+        self._indep_store(_u8(init), _u64(off), _d(jumps), _d(tot))
+        return PathSet(self._i_sites, self._i_nodes, init, off, jumps[:int(off[-1])].copy(), tot)
+
+    def indep_suffstats(self):
+        """compute_sufficient_statistics: AVERAGES over sites, [n_nodes, 2]."""
+        J, D = np.zeros(self._i_nodes * 2), np.zeros(self._i_nodes * 2)
+        self._indep_suffstats(self._i_nodes, _d(J), _d(D))
+        return J.reshape(-1, 2), D.reshape(-1, 2)
+
+    def indep_expectation(self, tree: Tree, rates2):
+        J, D = np.zeros(tree.n_nodes * 2), np.zeros(tree.n_nodes * 2)
+        self._indep_expectation(tree.n_nodes, _u64(tree.subtree_sizes), _u64(tree.parent_ids),
+                                _d(tree.branches), _d(np.ascontiguousarray(rates2, np.float64)), _d(J), _d(D))
+        return J.reshape(-1, 2), D.reshape(-1, 2)
+
+    def indep_update_paths(self, tree: Tree, rates2, seed: int) -> None:
+        self._indep_update_paths(tree.n_nodes, _u64(tree.subtree_sizes), _u64(tree.parent_ids),
+                                 _d(tree.branches), _d(np.ascontiguousarray(rates2, np.float64)), seed)
+
+    def indep_estimate(self, tree: Tree, J, D, rates2, with_branches: bool):
+        r = np.ascontiguousarray(rates2, np.float64).copy()
+        br = np.ascontiguousarray(tree.branches, np.float64).copy()
+        self._indep_estimate(tree.n_nodes, _u64(tree.subtree_sizes), _u64(tree.parent_ids), _d(br),
+                             _d(np.ascontiguousarray(J, np.float64).reshape(-1).copy()),
+                             _d(np.ascontiguousarray(D, np.float64).reshape(-1).copy()), _d(r),
+                             int(with_branches))
+        return r, br
 
     def read_paths_file(self, filename: str, timing: bool = False):
         """The reference's read_paths on a local-paths file (reference build only)."""

@@ -71,6 +71,26 @@ def make_cli():
     os.remove(out + "/mcem_b.paths")
 
 
+def make_init():
+    """epievo_initialization (site-independent EM + resampled starting paths) by the reference
+    binary: the deterministic EM trajectory of -s 1, and the final parameters over 12 seeds."""
+    out = os.path.join(HERE, "cli")
+    tree, states = os.path.join(out, "tree.nwk"), os.path.join(out, "sim.states")
+    r = sh([BIN + "/epievo_initialization", "-v", "-s", "1", "-i", "10", "-B", "5", "-o", out + "/_tmp.paths",
+            "-p", out + "/_tmp.param", tree, states])
+    em = [l for l in r.stderr.splitlines() if l.startswith("itr") or (l[:1].isdigit() and len(l.split()) == 3)]
+    open(out + "/init.log", "w").write("".join(l + "\n" for l in em))
+    rows = []
+    for seed in range(1, 13):
+        sh([BIN + "/epievo_initialization", "-s", str(seed), "-i", "10", "-B", "5", "-o", out + "/_tmp.paths",
+            "-p", out + "/_tmp.param", tree, states])
+        vals = [l.split()[1:] for l in open(out + "/_tmp.param")]
+        rows.append("%d\t%s\t%s\t%s\t%s\n" % (seed, vals[0][0], vals[0][1], vals[1][0], vals[1][1]))
+    open(out + "/init_seeds.tsv", "w").write("seed\tT00\tT11\tbaseline00\tbaseline11\n" + "".join(rows))
+    os.remove(out + "/_tmp.paths")
+    os.remove(out + "/_tmp.param")
+
+
 CASES = {"testtree": (ref_test_tree, 300, 3.0), "pair": (lambda: Tree.pair(1.0), 300, 1.0),
          "bal8": (lambda: Tree.balanced(8, 0.05), 200, 2.0),
          "bal32": (lambda: Tree.balanced(32, 0.05), 60, 3.0)}
@@ -121,6 +141,10 @@ def make_lib():
 
 if __name__ == "__main__":
     assert cpu_libs.ref_available(), "build oracle/_ref first: make -C oracle ref"
-    make_cli()
-    make_lib()
+    if "--init-only" in sys.argv:        # adds the epievo_initialization fixtures, keeps the rest
+        make_init()
+    else:
+        make_cli()
+        make_init()
+        make_lib()
     print("golden vectors written to", HERE)

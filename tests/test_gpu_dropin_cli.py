@@ -87,3 +87,48 @@ def test_sim_pairwise_b200(tmp_path):
     assert np.array_equal(ps.end_state()[1], leaf.astype(np.uint8))
     j = ps.jumps
     assert np.all((j > 0) & (j < 1.0))
+
+
+def _em_lines(text):
+    return [l.split() for l in text.splitlines() if l[:1].isdigit() and len(l.split()) == 3]
+
+
+def test_epievo_initialization_b200(tmp_path):
+    """prog/epievo_initialization.cpp compiled unchanged, linked with host/IndepSite_b200.cpp
+    instead of IndepSite.o.  (1) The site-independent EM (:407-420) is deterministic given the
+    seed (the heuristic starting paths come from the caller's mt19937 on the host): its verbose
+    rate trajectory must equal the CPU reference binary's (tests/golden/cli/init.log) to the
+    printed precision.  (2) The final parameters depend on the sampled histories: over 12 seeds
+    they must be distributed as the reference's (init_seeds.tsv; KS and Welch t, Bonferroni
+    alpha = 1e-3)."""
+    exe = need("epievo_initialization_b200")
+    tree, states = os.path.join(CLI, "tree.nwk"), os.path.join(CLI, "sim.states")
+    out, par = str(tmp_path / "i.paths"), str(tmp_path / "i.param")
+    r = subprocess.run([exe, "-v", "-s", "1", "-i", "10", "-B", "5", "-o", out, "-p", par, tree, states],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    want = _em_lines(open(os.path.join(CLI, "init.log")).read())
+    got = _em_lines(r.stderr)
+    assert len(got) == len(want) == 11
+    for a, b in zip(got, want):
+        assert a[0] == b[0]
+        assert np.allclose([float(a[1]), float(a[2])], [float(b[1]), float(b[2])], rtol=2e-6, atol=0)
+    ps = read_paths(out)                                  # a valid local-paths file over the leaf data
+    leaves = np.loadtxt(states, skiprows=1, dtype=int)[:, 1:]
+    names = open(states).readline().lstrip("#").split()
+    for v, nm in enumerate(ps.node_names):
+        if nm in ("C", "D", "F"):
+            assert np.array_equal(ps.end_state()[v], leaves[:, names.index(nm)])
+    gold = np.loadtxt(os.path.join(CLI, "init_seeds.tsv"), skiprows=1)[:, 1:]
+    rows = []
+    for seed in range(201, 213):
+        r = subprocess.run([exe, "-s", str(seed), "-i", "10", "-B", "5", "-o", out, "-p", par, tree, states],
+                           capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        vals = [l.split()[1:] for l in open(par)]
+        rows.append([float(vals[0][0]), float(vals[0][1]), float(vals[1][0]), float(vals[1][1])])
+    rows = np.array(rows)
+    for k, name in enumerate(("T00", "T11", "baseline00", "baseline11")):
+        p_ks = stats.ks_2samp(gold[:, k], rows[:, k]).pvalue
+        p_t = stats.ttest_ind(gold[:, k], rows[:, k], equal_var=False).pvalue
+        assert min(p_ks, p_t) > 1e-3/8, (name, p_ks, p_t, gold[:, k].mean(), rows[:, k].mean())
