@@ -1,2 +1,2 @@
 mkdir -p gpurun_out
-python -m pytest tests -m gpu -q > gpurun_out/pytest_gpu.log 2>&1; tail -25 gpurun_out/pytest_gpu.log
+python tools/indep_bench.py bal8 12500000 > gpurun_out/indep_bench.json 2> gpurun_out/indep_bench.err; tail -3 gpurun_out/indep_bench.err; cat gpurun_out/indep_bench.json
