@@ -83,6 +83,22 @@ merge_row(const Row &L, const Row &M, const Row &R, double tot, const StatsAcc &
   }
 }
 
+static __device__ __noinline__ void
+ss_drain(const PathView &pv, const uint8_t *state, int W, const double *branch, const StatsAcc &A,
+         const unsigned *queue, int n_take, uint64_t c0) {
+  const int lane = threadIdx.x & 31;
+  __syncwarp();
+  if (lane < n_take) {
+    const unsigned it = queue[lane];
+    const int bi = (int)(it >> 16);
+    const uint64_t s = c0 + (it & 0xffffu);
+    Row L, M, R;
+    load3(pv, state, W, bi, s, L, M, R);
+    merge_row(L, M, R, branch[bi + 1], A, bi);
+  }
+  __syncwarp();
+}
+
 __global__ void __launch_bounds__(SS_THREADS, 3)
 suffstats_kernel(const PathView pv, const uint8_t *state, int W, int n_br, const double *branch,
                  uint64_t lo, uint64_t hi, unsigned long long *acc) {
@@ -103,19 +119,12 @@ suffstats_kernel(const PathView pv, const uint8_t *state, int W, int n_br, const
   for (uint64_t ch = warp_id; ch < n_chunks; ch += n_warps) {
     const uint64_t c0 = lo + ch*chunk;
     int qn = 0;                                  // queue fill (warp-uniform)
-    // merge 32 queued rows (or the last qn), one per lane
+    // merge 32 queued rows (or the last qn), one per lane -- out of line: the merge is large
+    // and inlining it at every call site made the kernel 104 KB of SASS, with instruction
+    // fetch as its first stall reason
     auto drain = [&](int n_take) {
-      __syncwarp();
-      if (lane < n_take) {
-        const unsigned it = s_queue[qn - n_take + lane];
-        const int bi = (int)(it >> 16);
-        const uint64_t s = c0 + (it & 0xffffu);
-        Row L, M, R;
-        load3(pv, state, W, bi, s, L, M, R);
-        merge_row(L, M, R, branch[bi + 1], A, bi);
-      }
+      ss_drain(pv, state, W, branch, A, s_queue + (qn - n_take), n_take, c0);
       qn -= n_take;
-      __syncwarp();
     };
     for (int b0 = 0; b0 < n_br; b0 += SS_GROUP) {
       uint64_t packed[SS_GROUP];                 // per branch: eight 8-bit counters of event-free rows
