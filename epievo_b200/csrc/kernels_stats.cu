@@ -29,7 +29,7 @@ constexpr int SS_THREADS = 256;
 // One global atomic per (branch, triplet) per CTA.  acc layout per branch: [0..8) D
 // partial sums (double), [8..16) J counts, [16..24) event-free row counts.
 constexpr int SS_ITERS = 16;     // warp rows (of 32 sites) per chunk
-constexpr int SS_GROUP = 8;      // branches whose packed counters live in registers at once
+constexpr int SS_GROUP = 4;   // measured 1 / 2 / 3 / 4 / 8 / 14: 1.97 / 1.51 / 1.36 / 1.31 / 1.42 / 1.76 ms (load parallelism vs code size)      // branches whose packed counters live in registers at once
 constexpr int SS_QCAP = 96;      // queue entries per warp (drained in batches of 32)
 constexpr double SS_FIX = 1099511627776.0;   // 2^40
 
