@@ -125,9 +125,8 @@ int read_accepts(epv_ctx *c, uint64_t *n) {
 
 int do_suffstats(epv_ctx *c) {
   uint64_t lo, hi; interior(c, lo, hi);
-  launch_suffstats(c->view(c->cur), c->d_state, c->W, c->tree(), c->n_sites, lo, hi, c->d_J, c->d_D,
-                   c->d_ss, c->stream, c->sm_count);
-  c->launches += 2;
+  c->launches += launch_suffstats(c->view(c->cur), c->d_state, c->W, c->tree(), c->n_sites, lo, hi,
+                                  c->d_J, c->d_D, c->d_ss, c->stream, c->sm_count);
   c->stats_valid = true;
   return 0;
 }

@@ -26,18 +26,33 @@ constexpr int SS_THREADS = 256;
 //    tot_time * 2^-40: native integer atomics instead of fp64 CAS loops; the rounding is
 //    <= 2^-41 of a branch length per term, far inside the 1e-9 parity bound), J as
 //    integers.
-// One global atomic per (branch, triplet) per CTA.  acc layout per branch: [0..8) D
-// partial sums (double), [8..16) J counts, [16..24) event-free row counts.
+// One global atomic per (branch, triplet) per CTA, all of them integer, so the result does not
+// depend on the order in which CTAs (or the tile / generic kernels) finish.  acc layout per
+// branch: [0..8) low 32 bits of the fixed-point D sums, [8..16) J counts, [16..24) event-free
+// row counts, [24..32) high bits of the D sums.
 constexpr int SS_ITERS = 16;     // warp rows (of 32 sites) per chunk
 constexpr int SS_GROUP = 4;   // measured 1 / 2 / 3 / 4 / 8 / 14: 1.97 / 1.51 / 1.36 / 1.31 / 1.42 / 1.76 ms (load parallelism vs code size)      // branches whose packed counters live in registers at once
 constexpr int SS_QCAP = 96;      // queue entries per warp (drained in batches of 32)
 constexpr double SS_FIX = 1099511627776.0;   // 2^40
+constexpr int SS_ACC = 32;       // accumulator words per branch
 
 struct StatsAcc {
   long long *Dfix;     // [n_br*8] fixed-point D of rows with events
   unsigned *J;         // [n_br*8]
   unsigned *C;         // [n_br*8] event-free rows
 };
+
+__device__ __forceinline__ void
+flush_acc(const StatsAcc &A, int i, unsigned long long *acc) {
+  const int bi = i >> 3, t = i & 7;
+  const unsigned long long d = (unsigned long long)A.Dfix[i];
+  if (d) {
+    atomicAdd(acc + bi*SS_ACC + t, d & 0xffffffffull);
+    atomicAdd(acc + bi*SS_ACC + 24 + t, d >> 32);
+  }
+  if (A.J[i]) atomicAdd(acc + bi*SS_ACC + 8 + t, (unsigned long long)A.J[i]);
+  if (A.C[i]) atomicAdd(acc + bi*SS_ACC + 16 + t, (unsigned long long)A.C[i]);
+}
 
 __device__ __forceinline__ void
 load3(const PathView &pv, const uint8_t *state, int W, int bi, uint64_t s, Row &L, Row &M, Row &R) {
@@ -191,11 +206,144 @@ suffstats_kernel(const PathView pv, const uint8_t *state, int W, int n_br, const
   }
   __syncthreads();
   for (int i = threadIdx.x; i < n_br*8; i += SS_THREADS) {
-    const int bi = i >> 3, t = i & 7;
-    if (A.Dfix[i]) atomicAdd(reinterpret_cast<double *>(acc) + bi*24 + t,
-                             (double)A.Dfix[i]*(branch[bi + 1]/SS_FIX));
-    if (A.J[i]) atomicAdd(acc + bi*24 + 8 + t, (unsigned long long)A.J[i]);
-    if (A.C[i]) atomicAdd(acc + bi*24 + 16 + t, (unsigned long long)A.C[i]);
+    flush_acc(A, i, acc);
+  }
+}
+
+// ---- tile kernel: the interior of the shard, 128 rows x one branch per step ----------------
+// A warp owns a tile of 128 consecutive rows; lane i holds rows 4i..4i+3 of it (one 16-byte
+// load of the offsets per branch).  Everything that decides between the two kinds of rows is
+// done on 32-bit masks, bit i of mask j = row 4i+j ("strided" order: the right neighbour of
+// (i, j<3) is (i, j+1), of (i, 3) it is (i+1, 0), so neighbour masks are the other masks or a
+// one-bit shift of them, never a bit permutation):
+//   J_j   rows that hold a jump           ballot(o[j+1] != o[j])
+//   ev_j  rows whose triple has an event   J_j | J of the left row | J of the right row
+//   M_j   initial state on the branch      ballot(bit bi+1 of the site's state word)
+// Event-free rows: lane k < 8 counts the rows of triplet k with four popcounts
+// (pattern match = three xors against per-lane constants) -- about 25 thread instructions per
+// row against ~100 for the per-lane classification of suffstats_kernel.  Rows with events go
+// to the same per-warp queue and out-of-line merge as there.  The rows next to the shard's
+// ends (and trees wider than 64 nodes) stay with suffstats_kernel.
+constexpr int ST_THREADS = 256;
+constexpr int ST_ROWS = 128;     // rows per tile
+constexpr int ST_QCAP = 160;     // < 32 left over + up to 128 new entries per (tile, branch)
+#ifndef ST_G_
+#define ST_G_ 1
+#endif
+#ifndef ST_MINB_
+#define ST_MINB_ 4
+#endif
+#ifndef ST_PFD_
+#define ST_PFD_ 0
+#endif
+constexpr int ST_G = ST_G_;      // branches whose offset loads are issued together
+constexpr int ST_PFD = ST_PFD_;  // offset lines are prefetched into L1 this many branches ahead (4 lines per
+                                 // branch and tile; the pass is bound by load latency, not by bandwidth)
+
+__device__ __forceinline__ void prefetch_l1(const void *p) { asm volatile("prefetch.global.L1 [%0];" :: "l"(p)); }
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); }
+
+struct TileLoad { uint4 o; uint32_t el; uint2 er; };
+
+__global__ void __launch_bounds__(ST_THREADS, ST_MINB_)
+suffstats_tile_kernel(const PathView pv, const uint8_t *state, int W, int n_br, const double *branch,
+                      uint64_t r0, uint64_t n_tiles, unsigned long long *acc) {
+  extern __shared__ unsigned long long s_raw[];
+  StatsAcc A;
+  A.Dfix = reinterpret_cast<long long *>(s_raw);
+  A.J = reinterpret_cast<unsigned *>(s_raw + n_br*8);
+  A.C = A.J + n_br*8;
+  unsigned *s_queue = A.C + n_br*8 + (threadIdx.x >> 5)*ST_QCAP;
+  for (int i = threadIdx.x; i < n_br*8; i += ST_THREADS) { A.Dfix[i] = 0; A.J[i] = 0; A.C[i] = 0; }
+  __syncthreads();
+  constexpr unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const unsigned lt = (1u << lane) - 1u;
+  const int k = lane & 7;
+  const unsigned xl = (k & 4) ? 0u : ~0u, xm = (k & 2) ? 0u : ~0u, xr = (k & 1) ? 0u : ~0u;
+  const uint64_t warp_id = ((uint64_t)blockIdx.x*ST_THREADS + threadIdx.x) >> 5;
+  const uint64_t n_warps = ((uint64_t)gridDim.x*ST_THREADS) >> 5;
+  for (uint64_t tile = warp_id; tile < n_tiles; tile += n_warps) {
+    const uint64_t t0 = r0 + tile*ST_ROWS;       // first row of the tile (multiple of 4, >= 4)
+    const uint64_t s0 = pv.own_lo + t0;          // its site
+    const uint64_t w0 = state_word(state, W, s0 + 4*lane), w1 = state_word(state, W, s0 + 4*lane + 1),
+                   w2 = state_word(state, W, s0 + 4*lane + 2), w3 = state_word(state, W, s0 + 4*lane + 3);
+    const uint64_t we_l = state_word(state, W, s0 - 1), we_r = state_word(state, W, s0 + ST_ROWS);
+    int qn = 0;                                  // queue fill (warp-uniform)
+    if (ST_PFD > 0) {
+      // lane -> (branch lane/4, line lane%4) of the first 8 branches of this tile (L1) and of the
+      // warp's next tile (L2)
+      for (int p = lane; p < 4*ST_PFD && p < 4*n_br; p += 32)
+        prefetch_l1(pv.off + (uint64_t)(p >> 2)*pv.off_pitch + t0 + 32*(p & 3));
+      if (tile + n_warps < n_tiles)
+        for (int p = lane; p < 4*ST_PFD && p < 4*n_br; p += 32)
+          prefetch_l2(pv.off + (uint64_t)(p >> 2)*pv.off_pitch + t0 + n_warps*ST_ROWS + 32*(p & 3));
+    }
+    for (int b0 = 0; b0 < n_br; b0 += ST_G) {
+      if (ST_PFD > 0 && lane < 4*ST_G && b0 + ST_PFD + (lane >> 2) < n_br)
+        prefetch_l1(pv.off + (uint64_t)(b0 + ST_PFD + (lane >> 2))*pv.off_pitch + t0 + 32*(lane & 3));
+      TileLoad ld[ST_G];
+#pragma unroll
+      for (int g = 0; g < ST_G; ++g) {
+        ld[g].o = make_uint4(0, 0, 0, 0); ld[g].el = 0; ld[g].er = make_uint2(0, 0);
+        if (b0 + g < n_br) {
+          const uint32_t *ob = pv.off + (uint64_t)(b0 + g)*pv.off_pitch + t0;
+          ld[g].o = *reinterpret_cast<const uint4 *>(ob + 4*lane);
+          if (lane == 0) ld[g].el = *(ob - 1);
+          if (lane == 31) ld[g].er = *reinterpret_cast<const uint2 *>(ob + ST_ROWS);
+        }
+      }
+#pragma unroll
+      for (int g = 0; g < ST_G; ++g) {
+        const int bi = b0 + g;
+        if (bi >= n_br) break;
+        const uint4 o = ld[g].o;
+        uint32_t o4 = __shfl_down_sync(FULL, o.x, 1);
+        if (lane == 31) o4 = ld[g].er.x;
+        const unsigned J0 = __ballot_sync(FULL, o.y != o.x), J1 = __ballot_sync(FULL, o.z != o.y),
+                       J2 = __ballot_sync(FULL, o.w != o.z), J3 = __ballot_sync(FULL, o4 != o.w);
+#ifdef ST_JPF
+        // rows that hold jumps are merged later, from the queue: start fetching their jump times now
+        if ((o.y != o.x) | (o.z != o.y) | (o.w != o.z) | (o4 != o.w)) {
+          const double *jb = pv.jmp + pv.jbase[bi];
+          if (o.y != o.x) prefetch_l1(jb + o.x);
+          if (o.z != o.y) prefetch_l1(jb + o.y);
+          if (o.w != o.z) prefetch_l1(jb + o.z);
+          if (o4 != o.w) prefetch_l1(jb + o.w);
+        }
+#endif
+        // rows t0-1 (lane 0) and t0+128 (lane 31)
+        const unsigned me = __ballot_sync(FULL, lane == 0 ? ld[g].el != o.x
+                                                          : (lane == 31 && ld[g].er.y != ld[g].er.x));
+        const unsigned ev0 = J0 | J1 | (J3 << 1) | (me & 1u);
+        const unsigned ev1 = J0 | J1 | J2;
+        const unsigned ev2 = J1 | J2 | J3;
+        const unsigned ev3 = J2 | J3 | (J0 >> 1) | (me & 0x80000000u);
+        const int sh = bi + 1;
+        const unsigned M0 = __ballot_sync(FULL, (w0 >> sh) & 1), M1 = __ballot_sync(FULL, (w1 >> sh) & 1),
+                       M2 = __ballot_sync(FULL, (w2 >> sh) & 1), M3 = __ballot_sync(FULL, (w3 >> sh) & 1);
+        const unsigned L0 = (M3 << 1) | (unsigned)((we_l >> sh) & 1);
+        const unsigned R3 = (M0 >> 1) | ((unsigned)((we_r >> sh) & 1) << 31);
+        const unsigned c = __popc((L0 ^ xl) & (M0 ^ xm) & (M1 ^ xr) & ~ev0) +
+                           __popc((M0 ^ xl) & (M1 ^ xm) & (M2 ^ xr) & ~ev1) +
+                           __popc((M1 ^ xl) & (M2 ^ xm) & (M3 ^ xr) & ~ev2) +
+                           __popc((M2 ^ xl) & (M3 ^ xm) & (R3 ^ xr) & ~ev3);
+        if (lane < 8 && c) atomicAdd(&A.C[bi*8 + k], c);
+        const unsigned evs[4] = {ev0, ev1, ev2, ev3};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const unsigned ev = evs[j];
+          if ((ev >> lane) & 1) s_queue[qn + __popc(ev & lt)] = ((unsigned)bi << 16) | (unsigned)(4*lane + j);
+          qn += __popc(ev);
+        }
+        while (qn >= 32) { ss_drain(pv, state, W, branch, A, s_queue + (qn - 32), 32, s0); qn -= 32; }
+      }
+    }
+    if (qn > 0) ss_drain(pv, state, W, branch, A, s_queue, qn, s0);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < n_br*8; i += ST_THREADS) {
+    flush_acc(A, i, acc);
   }
 }
 
@@ -207,8 +355,8 @@ suffstats_fold_kernel(const unsigned long long *acc, const double *branch, int n
   if (i >= n_nodes*8) return;
   const int b = i >> 3, t = i & 7;
   if (b == 0) { J[i] = 0.0; D[i] = 0.0; return; }
-  const unsigned long long *a = acc + (b - 1)*24;
-  D[i] = __longlong_as_double((long long)a[t]) + (double)a[16 + t]*branch[b];
+  const unsigned long long *a = acc + (b - 1)*SS_ACC;
+  D[i] = ((double)a[24 + t]*4294967296.0 + (double)a[t])*(branch[b]/SS_FIX) + (double)a[16 + t]*branch[b];
   J[i] = (double)a[8 + t];
 }
 
@@ -321,24 +469,61 @@ scale_halo_kernel(double *hjmp, int n_br, const double *scale) {
 }  // namespace
 
 size_t
-suffstats_scratch_bytes(int n_nodes, int) { return (size_t)(n_nodes - 1)*24*8; }
+suffstats_scratch_bytes(int n_nodes, int) { return (size_t)(n_nodes - 1)*SS_ACC*8; }
+
+namespace {
 
 void
+launch_suffstats_generic(const PathView &pv, const uint8_t *state, int W, int n_br, const double *branch,
+                         uint64_t lo, uint64_t hi, unsigned long long *scratch, cudaStream_t st,
+                         int sm_count) {
+  const uint64_t n_chunks = (hi - lo + 32*SS_ITERS - 1)/(32*SS_ITERS);
+  const uint64_t want = (n_chunks + SS_THREADS/32 - 1)/(SS_THREADS/32);
+  const unsigned blocks = (unsigned)(want < (uint64_t)sm_count*8 ? want : (uint64_t)sm_count*8);
+  const size_t smem = (size_t)n_br*8*(8 + 4 + 4) + (SS_THREADS/32)*SS_QCAP*sizeof(unsigned);
+  cudaFuncSetAttribute(suffstats_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  suffstats_kernel<<<blocks, SS_THREADS, smem, st>>>(pv, state, W, n_br, branch, lo, hi, scratch);
+}
+
+}  // namespace
+
+// Returns the number of kernels launched.
+int
 launch_suffstats(const PathView &pv, const uint8_t *state, int W, const TreeDev &tree,
                  uint64_t, uint64_t lo, uint64_t hi, double *J, double *D,
                  unsigned long long *scratch, cudaStream_t st, int sm_count) {
   const int n_br = tree.n_nodes - 1;
-  cudaMemsetAsync(scratch, 0, (size_t)n_br*24*8, st);
+  int launches = 1;
+  cudaMemsetAsync(scratch, 0, (size_t)n_br*SS_ACC*8, st);
   if (hi > lo) {
-    const uint64_t n_chunks = (hi - lo + 32*SS_ITERS - 1)/(32*SS_ITERS);
-    const uint64_t want = (n_chunks + SS_THREADS/32 - 1)/(SS_THREADS/32);
-    const unsigned blocks = (unsigned)(want < (uint64_t)sm_count*8 ? want : (uint64_t)sm_count*8);
-    const size_t smem = (size_t)n_br*8*(8 + 4 + 4) + (SS_THREADS/32)*SS_QCAP*sizeof(unsigned);
-    cudaFuncSetAttribute(suffstats_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    suffstats_kernel<<<blocks, SS_THREADS, smem, st>>>(pv, state, W, n_br, tree.branch, lo, hi, scratch);
+    // rows [r0, r0 + 128 n_tiles): interior sites whose neighbours are owned, offsets r0-1 ..
+    // r0 + 128 n_tiles + 1 inside the CSR; the remainder on either side goes to the generic kernel
+    const uint64_t n_own = pv.own_hi - pv.own_lo;
+    const uint64_t first = lo > pv.own_lo ? lo - pv.own_lo : 0;
+    uint64_t r0 = (first + 3) & ~3ull;
+    if (r0 < 4) r0 = 4;
+    const uint64_t last = hi - pv.own_lo < n_own - 1 ? hi - pv.own_lo : n_own - 1;   // rows < last
+#ifdef SS_NO_TILE
+    const uint64_t n_tiles = 0;
+#else
+    const uint64_t n_tiles = (W <= 8 && n_own >= 2 && last > r0) ? (last - r0)/ST_ROWS : 0;
+#endif
+    if (n_tiles == 0) { launch_suffstats_generic(pv, state, W, n_br, tree.branch, lo, hi, scratch, st, sm_count); ++launches; }
+    else {
+      const uint64_t t_lo = pv.own_lo + r0, t_hi = t_lo + n_tiles*ST_ROWS;
+      const uint64_t want = (n_tiles + ST_THREADS/32 - 1)/(ST_THREADS/32);
+      const unsigned blocks = (unsigned)(want < (uint64_t)sm_count*8 ? want : (uint64_t)sm_count*8);
+      const size_t smem = (size_t)n_br*8*(8 + 4 + 4) + (ST_THREADS/32)*ST_QCAP*sizeof(unsigned);
+      cudaFuncSetAttribute(suffstats_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      suffstats_tile_kernel<<<blocks, ST_THREADS, smem, st>>>(pv, state, W, n_br, tree.branch, r0, n_tiles, scratch);
+      ++launches;
+      if (t_lo > lo) { launch_suffstats_generic(pv, state, W, n_br, tree.branch, lo, t_lo, scratch, st, sm_count); ++launches; }
+      if (hi > t_hi) { launch_suffstats_generic(pv, state, W, n_br, tree.branch, t_hi, hi, scratch, st, sm_count); ++launches; }
+    }
   }
   suffstats_fold_kernel<<<(tree.n_nodes*8 + 127)/128, 128, 0, st>>>(scratch, tree.branch,
                                                                    tree.n_nodes, J, D);
+  return launches;
 }
 
 void

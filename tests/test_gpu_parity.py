@@ -9,7 +9,10 @@ from synth import rel_close, synth_paths, ref_test_tree
 pytestmark = pytest.mark.gpu
 
 CASES = [("testtree", 3000, 1.0), ("testtree_dense", 500, 25.0), ("pair", 2000, 1.0),
-         ("bal8", 700, 2.0), ("bal32", 200, 3.0)]
+         ("bal8", 700, 2.0), ("bal32", 200, 3.0),
+         # sizes around the 128-row tiles of suffstats_tile_kernel (first tile starts at row 4)
+         ("testtree", 133, 2.0), ("testtree", 134, 2.0), ("testtree", 135, 8.0), ("testtree", 262, 1.0),
+         ("bal8", 1029, 1.0), ("bal32", 5000, 1.0), ("testtree", 40000, 1.0)]
 
 
 def make(case, n, density, seed=11):
