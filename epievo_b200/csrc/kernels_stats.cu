@@ -29,12 +29,13 @@ constexpr int SS_THREADS = 256;
 // One global atomic per (branch, triplet) per CTA, all of them integer, so the result does not
 // depend on the order in which CTAs (or the tile / generic kernels) finish.  acc layout per
 // branch: [0..8) low 32 bits of the fixed-point D sums, [8..16) J counts, [16..24) event-free
-// row counts, [24..32) high bits of the D sums.
+// row counts, [24..32) high bits of the D sums, [32..56) / [56..80) low / high bits of the tile
+// kernel's event-time sums by class (see there).
 constexpr int SS_ITERS = 16;     // warp rows (of 32 sites) per chunk
 constexpr int SS_GROUP = 4;   // measured 1 / 2 / 3 / 4 / 8 / 14: 1.97 / 1.51 / 1.36 / 1.31 / 1.42 / 1.76 ms (load parallelism vs code size)      // branches whose packed counters live in registers at once
 constexpr int SS_QCAP = 96;      // queue entries per warp (drained in batches of 32)
 constexpr double SS_FIX = 1099511627776.0;   // 2^40
-constexpr int SS_ACC = 32;       // accumulator words per branch
+constexpr int SS_ACC = 80;       // accumulator words per branch
 
 struct StatsAcc {
   long long *Dfix;     // [n_br*8] fixed-point D of rows with events
@@ -211,50 +212,138 @@ suffstats_kernel(const PathView pv, const uint8_t *state, int W, int n_br, const
 }
 
 // ---- tile kernel: the interior of the shard, 128 rows x one branch per step ----------------
-// A warp owns a tile of 128 consecutive rows; lane i holds rows 4i..4i+3 of it (one 16-byte
-// load of the offsets per branch).  Everything that decides between the two kinds of rows is
-// done on 32-bit masks, bit i of mask j = row 4i+j ("strided" order: the right neighbour of
-// (i, j<3) is (i, j+1), of (i, 3) it is (i+1, 0), so neighbour masks are the other masks or a
-// one-bit shift of them, never a bit permutation):
-//   J_j   rows that hold a jump           ballot(o[j+1] != o[j])
-//   ev_j  rows whose triple has an event   J_j | J of the left row | J of the right row
-//   M_j   initial state on the branch      ballot(bit bi+1 of the site's state word)
-// Event-free rows: lane k < 8 counts the rows of triplet k with four popcounts
-// (pattern match = three xors against per-lane constants) -- about 25 thread instructions per
-// row against ~100 for the per-lane classification of suffstats_kernel.  Rows with events go
-// to the same per-warp queue and out-of-line merge as there.  The rows next to the shard's
-// ends (and trees wider than 64 nodes) stay with suffstats_kernel.
+// Works from the identity (segment lengths telescope over the events of a row triple)
+//   D[trip] = tot * #{triples whose FINAL triplet is trip}
+//             + sum over events at time t of t * ([triplet before = trip] - [triplet after = trip]),
+// so no row triple is ever merged:
+//  * every row is classified by its final triplet with masks and popcounts.  A warp owns a tile
+//    of 128 consecutive rows; lane i holds rows 4i..4i+3 (one 16-byte load of the offsets per
+//    branch).  Bit i of mask j = row 4i+j ("strided" order: the right neighbour of (i, j<3) is
+//    (i, j+1), of (i, 3) it is (i+1, 0), so a neighbour mask is another mask or a one-bit shift
+//    of one, never a bit permutation).  F_j = ballot(initial state bit) ^ ballot(jump count odd)
+//    is the final state; lane k < 8 counts the rows of triplet k with four popcounts (pattern
+//    match = three xors against per-lane constants);
+//  * only rows that HOLD jumps (about 5 %; a row triple with an event is about 14 %) go to the
+//    per-warp queue.  A queued row is taken by one lane, which visits its jumps: the jump at time
+//    t is an event of the three triples centred on sites s-1, s, s+1; their triplets just before
+//    t come from the initial states of s-2..s+2 and, for the few neighbours that hold jumps
+//    themselves, the parity of their jumps before t (ties: the higher site first, as
+//    Path.cpp:275-281).  One fixed-point add of t per centre into the bin of (triplet before,
+//    which row jumped); suffstats_fold_kernel applies the +/-.  Bins are 64-bit integers in
+//    shared memory (CAS loops on this architecture), replicated in columns picked by the lane so
+//    that the lanes of a warp rarely meet in one bin.
+// The rows next to the shard's ends (and trees wider than 64 nodes) stay with suffstats_kernel.
 constexpr int ST_THREADS = 256;
 constexpr int ST_ROWS = 128;     // rows per tile
-constexpr int ST_QCAP = 160;     // < 32 left over + up to 128 new entries per (tile, branch)
-#ifndef ST_G_
-#define ST_G_ 1
-#endif
+constexpr int ST_QCAP = 168;     // < 32 left over + up to 130 new entries per (tile, branch)
 #ifndef ST_MINB_
 #define ST_MINB_ 4
 #endif
-#ifndef ST_PFD_
-#define ST_PFD_ 0
+#ifndef ST_WAVES_
+#define ST_WAVES_ 2
 #endif
-constexpr int ST_G = ST_G_;      // branches whose offset loads are issued together
-constexpr int ST_PFD = ST_PFD_;  // offset lines are prefetched into L1 this many branches ahead (4 lines per
-                                 // branch and tile; the pass is bound by load latency, not by bandwidth)
-
+#ifndef ST_PIPE_
+#define ST_PIPE_ 1
+#endif
 __device__ __forceinline__ void prefetch_l1(const void *p) { asm volatile("prefetch.global.L1 [%0];" :: "l"(p)); }
-__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); }
 
-struct TileLoad { uint4 o; uint32_t el; uint2 er; };
+struct TileShared {
+  long long *S;        // [n_br*24*cols] fixed-point sums of event times, class = trip_before*3 + which
+  unsigned *J;         // [n_br*8]
+  unsigned *C;         // [n_br*8] rows by final triplet
+  double *scale;       // [n_br] SS_FIX / tot_time
+  int col_shift;       // log2(cols)
+  uint64_t c_lo, c_hi; // sites whose triple this kernel accounts for
+};
+
+// Jumps of the row [p, p+n) before time t; with_ties: a jump AT t counts (the other row is to
+// the right of the one that jumps at t).
+__device__ __forceinline__ int
+jumps_before(const double *p, uint32_t n, double t, bool with_ties) {
+  int c = 0;
+  for (uint32_t i = 0; i < n; ++i) c += with_ties ? p[i] <= t : p[i] < t;
+  return c;
+}
+
+// Offsets of one (tile, branch) step: lane i holds rows 4i..4i+3; lane 0 also the offset before the
+// tile, lane 31 the two after it.
+struct TileStep { uint4 o; uint32_t el; uint2 er; };
+
+__device__ __forceinline__ TileStep
+load_step(const PathView &pv, uint64_t t0, int bi, int lane) {
+  const uint32_t *ob = pv.off + (uint64_t)bi*pv.off_pitch + t0;
+  TileStep r;
+  r.o = *reinterpret_cast<const uint4 *>(ob + 4*lane);
+  r.el = 0; r.er = make_uint2(0, 0);
+  if (lane == 0) r.el = *(ob - 1);
+  if (lane == 31) r.er = *reinterpret_cast<const uint2 *>(ob + ST_ROWS);
+  return r;
+}
+
+// (one call site, inlined: as an out-of-line call its by-reference arguments and the registers saved
+// around it were local-memory traffic twice the size of the kernel's global loads)
+__device__ __forceinline__ void
+st_drain(const PathView &pv, const uint8_t *state, int W, const TileShared &T, const unsigned *queue,
+         int n_take, uint64_t first_s0, uint64_t ord_stride) {
+  const int lane = threadIdx.x & 31;
+  __syncwarp();
+  if (lane < n_take) {
+    const unsigned it = queue[lane];
+    const int bi = (int)(it >> 26);
+    // code 0 = the row before the tile, 1..128 = its rows, 129 = the row after it
+    const uint64_t s = first_s0 + (uint64_t)((it >> 8) & 0x3ffffu)*ord_stride + (it & 0xffu) - 1;
+    const bool vL = s - 1 >= T.c_lo && s - 1 < T.c_hi, vM = s >= T.c_lo && s < T.c_hi,
+               vR = s + 1 >= T.c_lo && s + 1 < T.c_hi;
+    const uint32_t *o = pv.off + (uint64_t)bi*pv.off_pitch + (s - pv.own_lo);
+    const uint32_t o0 = o[0], o1 = o[1];
+    uint32_t a1 = o0, a2 = o0, c2 = o1, n2 = 0, n1 = 0, m1 = 0, m2 = 0;
+    int b2 = 0, b1 = 0, d1 = 0, d2 = 0;       // initial states of s-2, s-1, s+1, s+2
+    const int sh = bi + 1;
+    if (vL || vM) { a1 = o[-1]; n1 = o0 - a1; b1 = (int)((state_word(state, W, s - 1) >> sh) & 1); }
+    if (vL) { a2 = o[-2]; n2 = a1 - a2; b2 = (int)((state_word(state, W, s - 2) >> sh) & 1); }
+    if (vM || vR) { c2 = o[2]; m1 = c2 - o1; d1 = (int)((state_word(state, W, s + 1) >> sh) & 1); }
+    if (vR) { m2 = o[3] - c2; d2 = (int)((state_word(state, W, s + 2) >> sh) & 1); }
+    const int b0 = (int)((state_word(state, W, s) >> sh) & 1);
+    const double *jb = pv.jmp + pv.jbase[bi];
+    const double scale = T.scale[bi];
+    long long *S = T.S + ((size_t)bi*24 << T.col_shift) + (lane & ((1 << T.col_shift) - 1));
+    for (uint32_t k = 0; k < o1 - o0; ++k) {
+      const double t = jb[o0 + k];
+      const unsigned long long v = (unsigned long long)__double2ll_rn(t*scale);
+      const int own = b0 ^ (int)(k & 1);
+      int x2 = b2, x1 = b1, y1 = d1, y2 = d2;
+      if (n2) x2 ^= jumps_before(jb + a2, n2, t, false) & 1;
+      if (n1) x1 ^= jumps_before(jb + a1, n1, t, false) & 1;
+      if (m1) y1 ^= jumps_before(jb + o1, m1, t, true) & 1;
+      if (m2) y2 ^= jumps_before(jb + c2, m2, t, true) & 1;
+      if (vL) atomicAdd(reinterpret_cast<unsigned long long *>(S + (((x2*4 + x1*2 + own)*3 + 0) << T.col_shift)), v);
+      if (vM) {
+        const int tb = x1*4 + own*2 + y1;
+        atomicAdd(reinterpret_cast<unsigned long long *>(S + ((tb*3 + 1) << T.col_shift)), v);
+        atomicAdd(&T.J[bi*8 + tb], 1u);
+      }
+      if (vR) atomicAdd(reinterpret_cast<unsigned long long *>(S + (((own*4 + y1*2 + y2)*3 + 2) << T.col_shift)), v);
+    }
+  }
+  __syncwarp();
+}
 
 __global__ void __launch_bounds__(ST_THREADS, ST_MINB_)
 suffstats_tile_kernel(const PathView pv, const uint8_t *state, int W, int n_br, const double *branch,
-                      uint64_t r0, uint64_t n_tiles, unsigned long long *acc) {
+                      uint64_t r0, uint64_t n_tiles, int col_shift, unsigned long long *acc) {
   extern __shared__ unsigned long long s_raw[];
-  StatsAcc A;
-  A.Dfix = reinterpret_cast<long long *>(s_raw);
-  A.J = reinterpret_cast<unsigned *>(s_raw + n_br*8);
-  A.C = A.J + n_br*8;
-  unsigned *s_queue = A.C + n_br*8 + (threadIdx.x >> 5)*ST_QCAP;
-  for (int i = threadIdx.x; i < n_br*8; i += ST_THREADS) { A.Dfix[i] = 0; A.J[i] = 0; A.C[i] = 0; }
+  TileShared T;
+  const int n_bins = (n_br*24) << col_shift;
+  T.S = reinterpret_cast<long long *>(s_raw);
+  T.scale = reinterpret_cast<double *>(s_raw + n_bins);
+  T.J = reinterpret_cast<unsigned *>(s_raw + n_bins + n_br);
+  T.C = T.J + n_br*8;
+  T.col_shift = col_shift;
+  T.c_lo = pv.own_lo + r0; T.c_hi = T.c_lo + n_tiles*ST_ROWS;
+  unsigned *s_queue = T.C + n_br*8 + (threadIdx.x >> 5)*ST_QCAP;
+  for (int i = threadIdx.x; i < n_bins; i += ST_THREADS) T.S[i] = 0;
+  for (int i = threadIdx.x; i < n_br*8; i += ST_THREADS) { T.J[i] = 0; T.C[i] = 0; }
+  for (int i = threadIdx.x; i < n_br; i += ST_THREADS) T.scale[i] = SS_FIX/branch[i + 1];
   __syncthreads();
   constexpr unsigned FULL = 0xffffffffu;
   const int lane = threadIdx.x & 31;
@@ -263,91 +352,111 @@ suffstats_tile_kernel(const PathView pv, const uint8_t *state, int W, int n_br, 
   const unsigned xl = (k & 4) ? 0u : ~0u, xm = (k & 2) ? 0u : ~0u, xr = (k & 1) ? 0u : ~0u;
   const uint64_t warp_id = ((uint64_t)blockIdx.x*ST_THREADS + threadIdx.x) >> 5;
   const uint64_t n_warps = ((uint64_t)gridDim.x*ST_THREADS) >> 5;
-  for (uint64_t tile = warp_id; tile < n_tiles; tile += n_warps) {
+  // tile = warp_id + ord * n_warps: neighbouring tiles are read by neighbouring warps at about the
+  // same time (a contiguous span per warp was tried: 66 000 separate 512-byte streams, DRAM read
+  // traffic and latency both up).  Queue entries carry ord, so the queue runs on across tiles and
+  // only the last batch of a warp is partial.
+  const uint64_t first_s0 = pv.own_lo + r0 + warp_id*ST_ROWS, ord_stride = n_warps*ST_ROWS;
+  int qn = 0;                                    // queue fill (warp-uniform)
+  TileStep cur;
+#if ST_PIPE_
+  if (warp_id < n_tiles) cur = load_step(pv, r0 + warp_id*ST_ROWS, 0, lane);
+#endif
+  unsigned ord = 0;
+  for (uint64_t tile = warp_id; tile < n_tiles; tile += n_warps, ++ord) {
     const uint64_t t0 = r0 + tile*ST_ROWS;       // first row of the tile (multiple of 4, >= 4)
     const uint64_t s0 = pv.own_lo + t0;          // its site
     const uint64_t w0 = state_word(state, W, s0 + 4*lane), w1 = state_word(state, W, s0 + 4*lane + 1),
                    w2 = state_word(state, W, s0 + 4*lane + 2), w3 = state_word(state, W, s0 + 4*lane + 3);
     const uint64_t we_l = state_word(state, W, s0 - 1), we_r = state_word(state, W, s0 + ST_ROWS);
-    int qn = 0;                                  // queue fill (warp-uniform)
-    if (ST_PFD > 0) {
-      // lane -> (branch lane/4, line lane%4) of the first 8 branches of this tile (L1) and of the
-      // warp's next tile (L2)
-      for (int p = lane; p < 4*ST_PFD && p < 4*n_br; p += 32)
-        prefetch_l1(pv.off + (uint64_t)(p >> 2)*pv.off_pitch + t0 + 32*(p & 3));
-      if (tile + n_warps < n_tiles)
-        for (int p = lane; p < 4*ST_PFD && p < 4*n_br; p += 32)
-          prefetch_l2(pv.off + (uint64_t)(p >> 2)*pv.off_pitch + t0 + n_warps*ST_ROWS + 32*(p & 3));
-    }
-    for (int b0 = 0; b0 < n_br; b0 += ST_G) {
-      if (ST_PFD > 0 && lane < 4*ST_G && b0 + ST_PFD + (lane >> 2) < n_br)
-        prefetch_l1(pv.off + (uint64_t)(b0 + ST_PFD + (lane >> 2))*pv.off_pitch + t0 + 32*(lane & 3));
-      TileLoad ld[ST_G];
-#pragma unroll
-      for (int g = 0; g < ST_G; ++g) {
-        ld[g].o = make_uint4(0, 0, 0, 0); ld[g].el = 0; ld[g].er = make_uint2(0, 0);
-        if (b0 + g < n_br) {
-          const uint32_t *ob = pv.off + (uint64_t)(b0 + g)*pv.off_pitch + t0;
-          ld[g].o = *reinterpret_cast<const uint4 *>(ob + 4*lane);
-          if (lane == 0) ld[g].el = *(ob - 1);
-          if (lane == 31) ld[g].er = *reinterpret_cast<const uint2 *>(ob + ST_ROWS);
-        }
+    const unsigned tcode = ord << 8;
+    // the rows just outside the kernel's range hold events of the first / last triple inside it
+    const bool edge_l = tile == 0, edge_r = tile + 1 == n_tiles;
+    for (int bi = 0; bi < n_br; ++bi) {
+#if ST_PIPE_
+      // the loads of the next step (next branch, or the first branch of the warp's next tile) are
+      // issued before this step's are used
+      const uint4 o = cur.o; const uint32_t el = cur.el; const uint2 er = cur.er;
+      {
+        const bool wrap = bi + 1 == n_br;
+        if (!wrap || tile + n_warps < n_tiles)
+          cur = load_step(pv, wrap ? t0 + n_warps*ST_ROWS : t0, wrap ? 0 : bi + 1, lane);
       }
-#pragma unroll
-      for (int g = 0; g < ST_G; ++g) {
-        const int bi = b0 + g;
-        if (bi >= n_br) break;
-        const uint4 o = ld[g].o;
-        uint32_t o4 = __shfl_down_sync(FULL, o.x, 1);
-        if (lane == 31) o4 = ld[g].er.x;
-        const unsigned J0 = __ballot_sync(FULL, o.y != o.x), J1 = __ballot_sync(FULL, o.z != o.y),
-                       J2 = __ballot_sync(FULL, o.w != o.z), J3 = __ballot_sync(FULL, o4 != o.w);
+#else
+      cur = load_step(pv, t0, bi, lane);
+      const uint4 o = cur.o; const uint32_t el = cur.el; const uint2 er = cur.er;
+#endif
+      uint32_t o4 = __shfl_down_sync(FULL, o.x, 1);
+      if (lane == 31) o4 = er.x;
+      const uint32_t n0 = o.y - o.x, n1 = o.z - o.y, n2 = o.w - o.z, n3 = o4 - o.w;
+      const unsigned J0 = __ballot_sync(FULL, n0 != 0), J1 = __ballot_sync(FULL, n1 != 0),
+                     J2 = __ballot_sync(FULL, n2 != 0), J3 = __ballot_sync(FULL, n3 != 0);
+      // jump counts of rows t0-1 (lane 0) and t0+128 (lane 31)
+      const uint32_t ne = lane == 0 ? o.x - el : (lane == 31 ? er.y - er.x : 0u);
+      const unsigned pe = __ballot_sync(FULL, ne & 1);
+      const int sh = bi + 1;
+      unsigned F0 = __ballot_sync(FULL, ((w0 >> sh) ^ n0) & 1), F1 = __ballot_sync(FULL, ((w1 >> sh) ^ n1) & 1),
+               F2 = __ballot_sync(FULL, ((w2 >> sh) ^ n2) & 1), F3 = __ballot_sync(FULL, ((w3 >> sh) ^ n3) & 1);
+      const unsigned L0 = (F3 << 1) | (((unsigned)(we_l >> sh) ^ pe) & 1u);
+      const unsigned R3 = (F0 >> 1) | ((((unsigned)(we_r >> sh) << 31) ^ pe) & 0x80000000u);
+      const unsigned c = __popc((L0 ^ xl) & (F0 ^ xm) & (F1 ^ xr)) + __popc((F0 ^ xl) & (F1 ^ xm) & (F2 ^ xr)) +
+                         __popc((F1 ^ xl) & (F2 ^ xm) & (F3 ^ xr)) + __popc((F2 ^ xl) & (F3 ^ xm) & (R3 ^ xr));
+      if (lane < 8 && c) atomicAdd(&T.C[bi*8 + k], c);
+      const unsigned head = ((unsigned)bi << 26) | tcode;
+      if (J0 | J1 | J2 | J3) {
 #ifdef ST_JPF
-        // rows that hold jumps are merged later, from the queue: start fetching their jump times now
-        if ((o.y != o.x) | (o.z != o.y) | (o.w != o.z) | (o4 != o.w)) {
+        {                                        // the drain reads these rows' jump times: start now
           const double *jb = pv.jmp + pv.jbase[bi];
-          if (o.y != o.x) prefetch_l1(jb + o.x);
-          if (o.z != o.y) prefetch_l1(jb + o.y);
-          if (o.w != o.z) prefetch_l1(jb + o.z);
-          if (o4 != o.w) prefetch_l1(jb + o.w);
+          if (n0) prefetch_l1(jb + o.x);
+          if (n1) prefetch_l1(jb + o.y);
+          if (n2) prefetch_l1(jb + o.z);
+          if (n3) prefetch_l1(jb + o.w);
         }
 #endif
-        // rows t0-1 (lane 0) and t0+128 (lane 31)
-        const unsigned me = __ballot_sync(FULL, lane == 0 ? ld[g].el != o.x
-                                                          : (lane == 31 && ld[g].er.y != ld[g].er.x));
-        const unsigned ev0 = J0 | J1 | (J3 << 1) | (me & 1u);
-        const unsigned ev1 = J0 | J1 | J2;
-        const unsigned ev2 = J1 | J2 | J3;
-        const unsigned ev3 = J2 | J3 | (J0 >> 1) | (me & 0x80000000u);
-        const int sh = bi + 1;
-        const unsigned M0 = __ballot_sync(FULL, (w0 >> sh) & 1), M1 = __ballot_sync(FULL, (w1 >> sh) & 1),
-                       M2 = __ballot_sync(FULL, (w2 >> sh) & 1), M3 = __ballot_sync(FULL, (w3 >> sh) & 1);
-        const unsigned L0 = (M3 << 1) | (unsigned)((we_l >> sh) & 1);
-        const unsigned R3 = (M0 >> 1) | ((unsigned)((we_r >> sh) & 1) << 31);
-        const unsigned c = __popc((L0 ^ xl) & (M0 ^ xm) & (M1 ^ xr) & ~ev0) +
-                           __popc((M0 ^ xl) & (M1 ^ xm) & (M2 ^ xr) & ~ev1) +
-                           __popc((M1 ^ xl) & (M2 ^ xm) & (M3 ^ xr) & ~ev2) +
-                           __popc((M2 ^ xl) & (M3 ^ xm) & (R3 ^ xr) & ~ev3);
-        if (lane < 8 && c) atomicAdd(&A.C[bi*8 + k], c);
-        const unsigned evs[4] = {ev0, ev1, ev2, ev3};
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const unsigned ev = evs[j];
-          if ((ev >> lane) & 1) s_queue[qn + __popc(ev & lt)] = ((unsigned)bi << 16) | (unsigned)(4*lane + j);
-          qn += __popc(ev);
-        }
-        while (qn >= 32) { ss_drain(pv, state, W, branch, A, s_queue + (qn - 32), 32, s0); qn -= 32; }
+        if ((J0 >> lane) & 1) s_queue[qn + __popc(J0 & lt)] = head | (unsigned)(4*lane + 1);
+        qn += __popc(J0);
+        if ((J1 >> lane) & 1) s_queue[qn + __popc(J1 & lt)] = head | (unsigned)(4*lane + 2);
+        qn += __popc(J1);
+        if ((J2 >> lane) & 1) s_queue[qn + __popc(J2 & lt)] = head | (unsigned)(4*lane + 3);
+        qn += __popc(J2);
+        if ((J3 >> lane) & 1) s_queue[qn + __popc(J3 & lt)] = head | (unsigned)(4*lane + 4);
+        qn += __popc(J3);
+      }
+      if (edge_l | edge_r) {                     // warp-uniform, two tiles of the whole launch
+        const unsigned je = __ballot_sync(FULL, ne != 0) & ((edge_l ? 1u : 0u) | (edge_r ? 0x80000000u : 0u));
+        if ((je >> lane) & 1) s_queue[qn + __popc(je & lt)] = head | (lane == 0 ? 0u : (unsigned)(ST_ROWS + 1));
+        qn += __popc(je);
+      }
+      const bool last = bi + 1 == n_br && tile + n_warps >= n_tiles;   // this warp's last step
+      while (qn >= 32 || (last && qn > 0)) {
+        const int n_take = qn < 32 ? qn : 32;
+        st_drain(pv, state, W, T, s_queue + (qn - n_take), n_take, first_s0, ord_stride);
+        qn -= n_take;
       }
     }
-    if (qn > 0) ss_drain(pv, state, W, branch, A, s_queue, qn, s0);
   }
   __syncthreads();
+  // integer-only global accumulation; columns are summed here
+  for (int i = threadIdx.x; i < n_br*24; i += ST_THREADS) {
+    unsigned long long v = 0;
+    for (int cix = 0; cix < (1 << col_shift); ++cix) v += (unsigned long long)T.S[((size_t)i << col_shift) + cix];
+    if (v) {
+      const int bi = i/24, cls = i%24;
+      atomicAdd(acc + bi*SS_ACC + 32 + cls, v & 0xffffffffull);
+      atomicAdd(acc + bi*SS_ACC + 56 + cls, (unsigned long long)((long long)v >> 32));
+    }
+  }
   for (int i = threadIdx.x; i < n_br*8; i += ST_THREADS) {
-    flush_acc(A, i, acc);
+    const int bi = i >> 3, t = i & 7;
+    if (T.J[i]) atomicAdd(acc + bi*SS_ACC + 8 + t, (unsigned long long)T.J[i]);
+    if (T.C[i]) atomicAdd(acc + bi*SS_ACC + 16 + t, (unsigned long long)T.C[i]);
   }
 }
 
-// D[b][t] = partial + count*tot_time[b];  J[b][t] = count.  Row 0 (root) is zero.
+// D[b][t] = (row-merged partial sums + event-time sums with their signs) + count*tot_time[b];
+// J[b][t] = count.  Row 0 (root) is zero.  Event class (trip_before, which): which = 0 / 1 / 2 =
+// the right / middle / left row of the triple jumped, i.e. bit 1 / 2 / 4 of the triplet flips;
+// the time is added to D[trip_before] and taken from D[trip_before ^ flip].
 __global__ void
 suffstats_fold_kernel(const unsigned long long *acc, const double *branch, int n_nodes,
                       double *J, double *D) {
@@ -356,7 +465,14 @@ suffstats_fold_kernel(const unsigned long long *acc, const double *branch, int n
   const int b = i >> 3, t = i & 7;
   if (b == 0) { J[i] = 0.0; D[i] = 0.0; return; }
   const unsigned long long *a = acc + (b - 1)*SS_ACC;
-  D[i] = ((double)a[24 + t]*4294967296.0 + (double)a[t])*(branch[b]/SS_FIX) + (double)a[16 + t]*branch[b];
+  long long lo = (long long)a[t], hi = (long long)a[24 + t];
+#pragma unroll
+  for (int w = 0; w < 3; ++w) {
+    const int out = t*3 + w, in = (t ^ (1 << w))*3 + w;
+    lo += (long long)a[32 + out] - (long long)a[32 + in];
+    hi += (long long)a[56 + out] - (long long)a[56 + in];
+  }
+  D[i] = ((double)hi*4294967296.0 + (double)lo)*(branch[b]/SS_FIX) + (double)a[16 + t]*branch[b];
   J[i] = (double)a[8 + t];
 }
 
@@ -512,10 +628,16 @@ launch_suffstats(const PathView &pv, const uint8_t *state, int W, const TreeDev 
     else {
       const uint64_t t_lo = pv.own_lo + r0, t_hi = t_lo + n_tiles*ST_ROWS;
       const uint64_t want = (n_tiles + ST_THREADS/32 - 1)/(ST_THREADS/32);
-      const unsigned blocks = (unsigned)(want < (uint64_t)sm_count*8 ? want : (uint64_t)sm_count*8);
-      const size_t smem = (size_t)n_br*8*(8 + 4 + 4) + (ST_THREADS/32)*ST_QCAP*sizeof(unsigned);
+      const uint64_t wave = (uint64_t)sm_count*ST_MINB_*ST_WAVES_;
+      const unsigned blocks = (unsigned)(want < wave ? want : wave);
+      // bin columns: as many as fit in ~24 KB (fewer CAS retries), at least 2
+      int col_shift = 5;
+      while (col_shift > 1 && ((size_t)n_br*24*8 << col_shift) > 24*1024) --col_shift;
+      const size_t smem = ((size_t)n_br*24*8 << col_shift) + (size_t)n_br*8 + (size_t)n_br*8*(4 + 4) +
+                          (ST_THREADS/32)*ST_QCAP*sizeof(unsigned);
       cudaFuncSetAttribute(suffstats_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      suffstats_tile_kernel<<<blocks, ST_THREADS, smem, st>>>(pv, state, W, n_br, tree.branch, r0, n_tiles, scratch);
+      suffstats_tile_kernel<<<blocks, ST_THREADS, smem, st>>>(pv, state, W, n_br, tree.branch, r0, n_tiles,
+                                                             col_shift, scratch);
       ++launches;
       if (t_lo > lo) { launch_suffstats_generic(pv, state, W, n_br, tree.branch, lo, t_lo, scratch, st, sm_count); ++launches; }
       if (hi > t_hi) { launch_suffstats_generic(pv, state, W, n_br, tree.branch, t_hi, hi, scratch, st, sm_count); ++launches; }
