@@ -239,11 +239,14 @@ constexpr int ST_QCAP = 168;     // < 32 left over + up to 130 new entries per (
 #ifndef ST_MINB_
 #define ST_MINB_ 4
 #endif
+#ifndef ST_BINKB_
+#define ST_BINKB_ 24
+#endif
 #ifndef ST_WAVES_
 #define ST_WAVES_ 2
 #endif
 #ifndef ST_PIPE_
-#define ST_PIPE_ 1
+#define ST_PIPE_ 0
 #endif
 __device__ __forceinline__ void prefetch_l1(const void *p) { asm volatile("prefetch.global.L1 [%0];" :: "l"(p)); }
 
@@ -256,22 +259,12 @@ struct TileShared {
   uint64_t c_lo, c_hi; // sites whose triple this kernel accounts for
 };
 
-// Jumps of the row [p, p+n) before time t; with_ties: a jump AT t counts (the other row is to
-// the right of the one that jumps at t).
-__device__ __forceinline__ int
-jumps_before(const double *p, uint32_t n, double t, bool with_ties) {
-  int c = 0;
-  for (uint32_t i = 0; i < n; ++i) c += with_ties ? p[i] <= t : p[i] < t;
-  return c;
-}
-
 // Offsets of one (tile, branch) step: lane i holds rows 4i..4i+3; lane 0 also the offset before the
 // tile, lane 31 the two after it.
 struct TileStep { uint4 o; uint32_t el; uint2 er; };
 
 __device__ __forceinline__ TileStep
-load_step(const PathView &pv, uint64_t t0, int bi, int lane) {
-  const uint32_t *ob = pv.off + (uint64_t)bi*pv.off_pitch + t0;
+load_step(const uint32_t *ob, int lane) {      // ob = the branch's offset of the tile's first row
   TileStep r;
   r.o = *reinterpret_cast<const uint4 *>(ob + 4*lane);
   r.el = 0; r.er = make_uint2(0, 0);
@@ -296,26 +289,36 @@ st_drain(const PathView &pv, const uint8_t *state, int W, const TileShared &T, c
                vR = s + 1 >= T.c_lo && s + 1 < T.c_hi;
     const uint32_t *o = pv.off + (uint64_t)bi*pv.off_pitch + (s - pv.own_lo);
     const uint32_t o0 = o[0], o1 = o[1];
-    uint32_t a1 = o0, a2 = o0, c2 = o1, n2 = 0, n1 = 0, m1 = 0, m2 = 0;
+    // rows s-2, s-1, s, s+1, s+2 are [a2, a1), [a1, o0), [o0, o1), [o1, c2), [c2, e2) of the branch's
+    // jump times; a neighbour that no valid centre needs gets an empty range
+    uint32_t a1 = o0, a2 = o0, c2 = o1, e2 = o1;
     int b2 = 0, b1 = 0, d1 = 0, d2 = 0;       // initial states of s-2, s-1, s+1, s+2
     const int sh = bi + 1;
-    if (vL || vM) { a1 = o[-1]; n1 = o0 - a1; b1 = (int)((state_word(state, W, s - 1) >> sh) & 1); }
-    if (vL) { a2 = o[-2]; n2 = a1 - a2; b2 = (int)((state_word(state, W, s - 2) >> sh) & 1); }
-    if (vM || vR) { c2 = o[2]; m1 = c2 - o1; d1 = (int)((state_word(state, W, s + 1) >> sh) & 1); }
-    if (vR) { m2 = o[3] - c2; d2 = (int)((state_word(state, W, s + 2) >> sh) & 1); }
+    if (vL || vM) { a1 = o[-1]; a2 = a1; b1 = (int)((state_word(state, W, s - 1) >> sh) & 1); }
+    if (vL) { a2 = o[-2]; b2 = (int)((state_word(state, W, s - 2) >> sh) & 1); }
+    if (vM || vR) { c2 = o[2]; e2 = c2; d1 = (int)((state_word(state, W, s + 1) >> sh) & 1); }
+    if (vR) { e2 = o[3]; d2 = (int)((state_word(state, W, s + 2) >> sh) & 1); }
     const int b0 = (int)((state_word(state, W, s) >> sh) & 1);
     const double *jb = pv.jmp + pv.jbase[bi];
     const double scale = T.scale[bi];
     long long *S = T.S + ((size_t)bi*24 << T.col_shift) + (lane & ((1 << T.col_shift) - 1));
+    const uint32_t nl = o0 - a2, nn = nl + (e2 - o1);
     for (uint32_t k = 0; k < o1 - o0; ++k) {
       const double t = jb[o0 + k];
       const unsigned long long v = (unsigned long long)__double2ll_rn(t*scale);
       const int own = b0 ^ (int)(k & 1);
-      int x2 = b2, x1 = b1, y1 = d1, y2 = d2;
-      if (n2) x2 ^= jumps_before(jb + a2, n2, t, false) & 1;
-      if (n1) x1 ^= jumps_before(jb + a1, n1, t, false) & 1;
-      if (m1) y1 ^= jumps_before(jb + o1, m1, t, true) & 1;
-      if (m2) y2 ^= jumps_before(jb + c2, m2, t, true) & 1;
+      // parity of the neighbours' jumps before t, one flat loop over all four rows (ties: a row to
+      // the right jumps first)
+      unsigned fl = 0;
+      for (uint32_t j = 0; j < nn; ++j) {
+        const bool left = j < nl;
+        const uint32_t i = left ? a2 + j : o1 + (j - nl);
+        const double q = jb[i];
+        const bool before = left ? q < t : q <= t;
+        fl ^= (unsigned)before << (left ? (int)(i >= a1) : 2 + (int)(i >= c2));
+      }
+      const int x2 = b2 ^ (int)(fl & 1), x1 = b1 ^ (int)((fl >> 1) & 1), y1 = d1 ^ (int)((fl >> 2) & 1),
+                y2 = d2 ^ (int)(fl >> 3);
       if (vL) atomicAdd(reinterpret_cast<unsigned long long *>(S + (((x2*4 + x1*2 + own)*3 + 0) << T.col_shift)), v);
       if (vM) {
         const int tb = x1*4 + own*2 + y1;
@@ -328,6 +331,7 @@ st_drain(const PathView &pv, const uint8_t *state, int W, const TileShared &T, c
   __syncwarp();
 }
 
+template <typename WT>           // state bits of one site: uint32_t up to 32 nodes, else uint64_t
 __global__ void __launch_bounds__(ST_THREADS, ST_MINB_)
 suffstats_tile_kernel(const PathView pv, const uint8_t *state, int W, int n_br, const double *branch,
                       uint64_t r0, uint64_t n_tiles, int col_shift, unsigned long long *acc) {
@@ -359,16 +363,18 @@ suffstats_tile_kernel(const PathView pv, const uint8_t *state, int W, int n_br, 
   const uint64_t first_s0 = pv.own_lo + r0 + warp_id*ST_ROWS, ord_stride = n_warps*ST_ROWS;
   int qn = 0;                                    // queue fill (warp-uniform)
   TileStep cur;
+  const uint32_t *p_tile = pv.off + r0 + warp_id*ST_ROWS;    // branch 0, first row of the warp's tile
 #if ST_PIPE_
-  if (warp_id < n_tiles) cur = load_step(pv, r0 + warp_id*ST_ROWS, 0, lane);
+  if (warp_id < n_tiles) cur = load_step(p_tile, lane);
 #endif
   unsigned ord = 0;
-  for (uint64_t tile = warp_id; tile < n_tiles; tile += n_warps, ++ord) {
+  for (uint64_t tile = warp_id; tile < n_tiles; tile += n_warps, ++ord, p_tile += ord_stride) {
+    const uint32_t *p_step = p_tile;
     const uint64_t t0 = r0 + tile*ST_ROWS;       // first row of the tile (multiple of 4, >= 4)
     const uint64_t s0 = pv.own_lo + t0;          // its site
-    const uint64_t w0 = state_word(state, W, s0 + 4*lane), w1 = state_word(state, W, s0 + 4*lane + 1),
-                   w2 = state_word(state, W, s0 + 4*lane + 2), w3 = state_word(state, W, s0 + 4*lane + 3);
-    const uint64_t we_l = state_word(state, W, s0 - 1), we_r = state_word(state, W, s0 + ST_ROWS);
+    const WT w0 = (WT)state_word(state, W, s0 + 4*lane), w1 = (WT)state_word(state, W, s0 + 4*lane + 1),
+             w2 = (WT)state_word(state, W, s0 + 4*lane + 2), w3 = (WT)state_word(state, W, s0 + 4*lane + 3);
+    const WT we_l = (WT)state_word(state, W, s0 - 1), we_r = (WT)state_word(state, W, s0 + ST_ROWS);
     const unsigned tcode = ord << 8;
     // the rows just outside the kernel's range hold events of the first / last triple inside it
     const bool edge_l = tile == 0, edge_r = tile + 1 == n_tiles;
@@ -379,11 +385,12 @@ suffstats_tile_kernel(const PathView pv, const uint8_t *state, int W, int n_br, 
       const uint4 o = cur.o; const uint32_t el = cur.el; const uint2 er = cur.er;
       {
         const bool wrap = bi + 1 == n_br;
-        if (!wrap || tile + n_warps < n_tiles)
-          cur = load_step(pv, wrap ? t0 + n_warps*ST_ROWS : t0, wrap ? 0 : bi + 1, lane);
+        p_step = wrap ? p_tile + ord_stride : p_step + pv.off_pitch;
+        if (!wrap || tile + n_warps < n_tiles) cur = load_step(p_step, lane);
       }
 #else
-      cur = load_step(pv, t0, bi, lane);
+      cur = load_step(p_step, lane);
+      p_step += pv.off_pitch;
       const uint4 o = cur.o; const uint32_t el = cur.el; const uint2 er = cur.er;
 #endif
       uint32_t o4 = __shfl_down_sync(FULL, o.x, 1);
@@ -404,23 +411,14 @@ suffstats_tile_kernel(const PathView pv, const uint8_t *state, int W, int n_br, 
       if (lane < 8 && c) atomicAdd(&T.C[bi*8 + k], c);
       const unsigned head = ((unsigned)bi << 26) | tcode;
       if (J0 | J1 | J2 | J3) {
-#ifdef ST_JPF
-        {                                        // the drain reads these rows' jump times: start now
-          const double *jb = pv.jmp + pv.jbase[bi];
-          if (n0) prefetch_l1(jb + o.x);
-          if (n1) prefetch_l1(jb + o.y);
-          if (n2) prefetch_l1(jb + o.z);
-          if (n3) prefetch_l1(jb + o.w);
-        }
-#endif
-        if ((J0 >> lane) & 1) s_queue[qn + __popc(J0 & lt)] = head | (unsigned)(4*lane + 1);
-        qn += __popc(J0);
-        if ((J1 >> lane) & 1) s_queue[qn + __popc(J1 & lt)] = head | (unsigned)(4*lane + 2);
-        qn += __popc(J1);
-        if ((J2 >> lane) & 1) s_queue[qn + __popc(J2 & lt)] = head | (unsigned)(4*lane + 3);
-        qn += __popc(J2);
-        if ((J3 >> lane) & 1) s_queue[qn + __popc(J3 & lt)] = head | (unsigned)(4*lane + 4);
-        qn += __popc(J3);
+        // queue order: by lane, then by row (any order will do; one prefix per lane, not per mask)
+        int q = qn + __popc(J0 & lt) + __popc(J1 & lt) + __popc(J2 & lt) + __popc(J3 & lt);
+        const unsigned e = head | (unsigned)(4*lane + 1);
+        if (n0) s_queue[q++] = e;
+        if (n1) s_queue[q++] = e + 1;
+        if (n2) s_queue[q++] = e + 2;
+        if (n3) s_queue[q] = e + 3;
+        qn += __popc(J0) + __popc(J1) + __popc(J2) + __popc(J3);
       }
       if (edge_l | edge_r) {                     // warp-uniform, two tiles of the whole launch
         const unsigned je = __ballot_sync(FULL, ne != 0) & ((edge_l ? 1u : 0u) | (edge_r ? 0x80000000u : 0u));
@@ -632,12 +630,12 @@ launch_suffstats(const PathView &pv, const uint8_t *state, int W, const TreeDev 
       const unsigned blocks = (unsigned)(want < wave ? want : wave);
       // bin columns: as many as fit in ~24 KB (fewer CAS retries), at least 2
       int col_shift = 5;
-      while (col_shift > 1 && ((size_t)n_br*24*8 << col_shift) > 24*1024) --col_shift;
+      while (col_shift > 1 && ((size_t)n_br*24*8 << col_shift) > ST_BINKB_*1024) --col_shift;
       const size_t smem = ((size_t)n_br*24*8 << col_shift) + (size_t)n_br*8 + (size_t)n_br*8*(4 + 4) +
                           (ST_THREADS/32)*ST_QCAP*sizeof(unsigned);
-      cudaFuncSetAttribute(suffstats_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      suffstats_tile_kernel<<<blocks, ST_THREADS, smem, st>>>(pv, state, W, n_br, tree.branch, r0, n_tiles,
-                                                             col_shift, scratch);
+      auto kernel = W <= 4 ? suffstats_tile_kernel<uint32_t> : suffstats_tile_kernel<uint64_t>;
+      cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      kernel<<<blocks, ST_THREADS, smem, st>>>(pv, state, W, n_br, tree.branch, r0, n_tiles, col_shift, scratch);
       ++launches;
       if (t_lo > lo) { launch_suffstats_generic(pv, state, W, n_br, tree.branch, lo, t_lo, scratch, st, sm_count); ++launches; }
       if (hi > t_hi) { launch_suffstats_generic(pv, state, W, n_br, tree.branch, t_hi, hi, scratch, st, sm_count); ++launches; }
