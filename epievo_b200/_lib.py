@@ -43,6 +43,8 @@ SIGNATURES = {
     "epv_scale_jump_times": (C.c_int, [ctx_p, dp]),
     "epv_mcem_iteration": (C.c_int, [ctx_p, u64, u64, u64, u64, C.c_int, C.c_double, dp, dp, dp, dp,
                                      dp, dp]),
+    "epv_simulate": (C.c_int, [ctx_p, u64, u8p, u64, u64p]),
+    "epv_simulate_fetch": (C.c_int, [ctx_p, u8p, u64p, dp]),
     "epv_pass": (C.c_int, [ctx_p, C.c_int, u64, u64]),
     "epv_accept_count": (C.c_int, [ctx_p, C.c_int, u64p]),
     "epv_halo_record_bytes": (C.c_int, [ctx_p, u64p]),

@@ -100,6 +100,7 @@ void epv_destroy(epv_ctx *c) {
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
   free_paths(c);
+  sim_release(c);
   cudaFree(c->d_parent); cudaFree(c->d_subtree); cudaFree(c->d_branch);
   cudaFree(c->d_err); cudaFree(c->d_nacc); cudaFree(c->d_ticket); cudaFree(c->d_scratch_ctr);
   cudaFree(c->d_stg_ctr); cudaFree(c->d_itab); cudaFree(c->d_iacc);

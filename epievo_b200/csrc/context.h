@@ -69,6 +69,9 @@ struct epv_ctx {
   uint16_t *d_hcnt = nullptr;               // [2*HALO_W][n_br]
   double *d_hjmp = nullptr;                 // [2*HALO_W][n_br][HALO_K]
 
+  // result of epv_simulate until epv_simulate_fetch (api_sim.cu)
+  void *sim = nullptr;
+
   // instrumentation
   uint64_t launches = 0, mh_launches = 0;
   bool timing = false;
@@ -99,6 +102,7 @@ namespace epv {
 int fail(epv_ctx *c, const std::string &msg);
 int check_cuda(epv_ctx *c, cudaError_t e, const char *what);
 void free_paths(epv_ctx *c);
-int check_device_flags(epv_ctx *c);   // reads d_err, turns sticky flags into an error
+int check_device_flags(epv_ctx *c);
+void sim_release(epv_ctx *c);          // frees what epv_simulate left on the device   // reads d_err, turns sticky flags into an error
 }
 #define EPV_CUDA(c, call) do { if (int _r = epv::check_cuda((c), (call), #call)) return _r; } while (0)

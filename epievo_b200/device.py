@@ -236,6 +236,21 @@ class Context:
     def indep_update_paths(self, rates2, seed: int, iteration: int = 0):
         self._ck(self.lib.epv_indep_update_paths(self.h, _d(_f64(rates2)), seed, iteration))
 
+    # -- forward simulation (epievo_sim -> global_jumps_to_paths) --------------------------
+    def simulate(self, n_sites: int, seed: int, tot_time, root_states=None, node_names=()) -> PathSet:
+        """Histories of n_sites evolved down the context's tree under its model; root drawn from
+        the horizontal chain unless given.  tot_time: the tree's branch lengths [n_nodes]."""
+        nj = C.c_uint64()
+        root = None if root_states is None else _u8(np.ascontiguousarray(root_states, np.uint8))
+        self._ck(self.lib.epv_simulate(self.h, n_sites, root, seed, C.byref(nj)))
+        init = np.zeros(n_sites * self.n_nodes, np.uint8)
+        off = np.zeros(n_sites * self.n_nodes + 1, np.uint64)
+        jumps = np.zeros(max(1, nj.value))
+        self._ck(self.lib.epv_simulate_fetch(self.h, _u8(init), _u64(off), _d(jumps)))
+        tt = _f64(tot_time).copy()
+        tt[0] = 0.0
+        return PathSet(n_sites, self.n_nodes, init, off, jumps[:nj.value].copy(), tt, list(node_names))
+
     # -- parity probes ----------------------------------------------------------------
     def site_debug(self, site: int, cap: int = 4096):
         nn = self.n_nodes

@@ -224,6 +224,22 @@ void epv_indep_estimate_rates_and_branches(uint64_t n_nodes, const double *J,
                                            const double *D, double *rates,
                                            double *branches);
 
+/* ---- forward simulation of histories --------------------------------- */
+/* replaces epievo_sim's simulation (prog/epievo_sim.cpp:102-152 sample_jump, :326-356 the loop
+ * over nodes; TripletSampler.cpp) followed by global_jumps_to_paths: evolves a root sequence down
+ * the tree set with epv_set_tree under the triplet rates set with epv_set_model, every interior
+ * site flipping at rate[left, self, right], the two end sites fixed.  Same law as the reference's
+ * global Gillespie simulation (thinning of per-site candidate events, decided in time order
+ * between neighbours), not the same random stream.  root_states: n_sites bytes (0/1), or NULL to
+ * draw the root from the horizontal chain T (sample_state_sequence, EpiEvoModel.cpp:282-298).
+ * Philox streams keyed (seed; candidate, site, node): the result depends on seed only.
+ * The histories stay on the device; *n_jumps tells the size of the jumps array to fetch. */
+int epv_simulate(epv_ctx *ctx, uint64_t n_sites, const uint8_t *root_states, uint64_t seed,
+                 uint64_t *n_jumps);
+/* copies the result out in the epv_upload_paths exchange format: init_state [n_nodes][n_sites],
+ * row_off [n_nodes*n_sites + 1] (root rows empty), jumps [n_jumps]; frees the device copy. */
+int epv_simulate_fetch(epv_ctx *ctx, uint8_t *init_state, uint64_t *row_off, double *jumps);
+
 /* ---- local-paths text files (host only, multi-threaded) ------------- */
 /* replaces read_paths (Path.cpp:123-148): parses the file with n_threads threads
  * (<= 0: all cores) into an opaque handle and reports the sizes; epv_pathfile_get fills
