@@ -23,6 +23,7 @@ void free_paths(epv_ctx *c) {
   cudaFree(c->d_jbase); cudaFree(c->d_jcap); cudaFree(c->d_state); cudaFree(c->d_tri);
   cudaFree(c->d_desc); cudaFree(c->d_hcnt); cudaFree(c->d_hjmp);
   cudaFree(c->d_stage_init); cudaFree(c->d_stage_off); cudaFree(c->d_stg_off); cudaFree(c->d_stg);
+  cudaFree(c->d_ovf_list); c->d_ovf_list = nullptr;
   c->d_stg_off = nullptr; c->d_stg = nullptr;
   c->d_hcnt = nullptr; c->d_hjmp = nullptr; c->d_stage_init = nullptr; c->d_stage_off = nullptr;
   c->d_jbase = c->d_jcap = nullptr; c->d_state = nullptr; c->d_tri = nullptr;

@@ -55,6 +55,7 @@ int alloc_stage(epv_ctx *c) {
   EPV_CUDA(c, cudaMalloc(&c->d_stg, cap*sizeof(double)));
   c->stg_cap = cap;
   if (!c->d_stg_off) EPV_CUDA(c, cudaMalloc(&c->d_stg_off, c->n_groups*sizeof(uint32_t)));
+  if (!c->d_ovf_list) EPV_CUDA(c, cudaMalloc(&c->d_ovf_list, (c->n_groups + 1)*sizeof(uint32_t)));
   return 0;
 }
 

@@ -40,6 +40,7 @@ struct epv_ctx {
 
   // staging of accepted proposals between the update and the rebuild kernel
   uint32_t *d_stg_off = nullptr;             // [n_groups]
+  uint32_t *d_ovf_list = nullptr;            // [1 + n_groups] groups deferred by the main update launch
   double *d_stg = nullptr;
   unsigned long long stg_cap = 0, *d_stg_ctr = nullptr;
   uint64_t n_groups = 0;

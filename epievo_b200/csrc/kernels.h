@@ -41,6 +41,8 @@ struct PassArgs {
   uint64_t n_groups;          // groups of 3 sites covering the local sites
   // groups one launch works on: index i < g_count maps to group g_first + i (+ g_skip when i >= g_split)
   uint64_t g_first, g_split, g_skip, g_count;
+  uint32_t *ovf_list;         // [1 + n_groups]: count, then the groups the main update launch deferred
+  int list_mode;              // the launch works on ovf_list instead of a group range
   uint32_t *stage_off;        // [n_groups] offset into stage, or rejected / empty marker
   double *stage;              // blobs: ceil(n_br/4) words of u16 jump counts + jump times
   unsigned long long *stage_ctr;

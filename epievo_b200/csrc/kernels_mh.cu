@@ -17,6 +17,8 @@
 // look-back spin: tiles whose updates finished early waited, holding their SM slots, for
 // the slowest earlier tile (update time varies with the rows' jump counts).  Splitting
 // costs one staging round trip of the accepted proposals (a few % of the row bytes).
+#include <cstdlib>
+
 #include "kernels.h"
 #include "mh_flat.cuh"
 #include "scan.cuh"
@@ -26,6 +28,12 @@ namespace epv {
 namespace {
 
 constexpr uint32_t STG_REJECTED = 0xffffffffu, STG_EMPTY = 0xfffffffeu;
+constexpr unsigned MH_OVF_BLOCKS = 296;     // grid of the overflow launch (grid-stride over the list)
+
+// The main update launch defers the sites its flat routine cannot finish to a second launch
+// (see mh_update_group).  Measured ms per pass, deferred vs inline fallback: 8-leaf tree 5.18 vs
+// 5.48, 4-branch test tree 5.64 vs 6.45, 32-leaf tree 8.73 vs 7.54 -- so only up to 16 nodes.
+__host__ __device__ constexpr bool mh_defer(int maxn) { return maxn <= 16; }
 
 __device__ __forceinline__ int stage_header_words(int n_br) { return (n_br + 3) >> 2; }
 
@@ -41,20 +49,21 @@ __host__ __device__ constexpr int mh_minblocks(int maxn) { return maxn <= 16 ? 4
 // jump-queue slots per thread (shared memory: 24 B each)
 __host__ __device__ constexpr int mh_qcap(int maxn) { return maxn <= 16 ? 8 : maxn <= 64 ? 16 : 24; }
 
-template <int MAXN, int MAXJ, bool HALO>
-__global__ void __launch_bounds__(MH_THREADS, mh_minblocks(MAXN))
-mh_update_kernel(const PassArgs a) {
-  __shared__ ModelParams s_mp;
-  __shared__ CtxTables s_tb;
-  extern __shared__ unsigned long long s_dyn[];    // [MH_THREADS*QCAP] QSlot, then [MH_THREADS] int
+// The update of group g's site of the pass's colour, and the staging of its rows.
+// DEFER (the halo-free main launch of trees up to 16 nodes): the flat routine is tried once; a site whose proposal does
+// not fit the per-thread buffer (-1) or whose neighbours' intervals do not fit the per-thread
+// stack (-3) is appended to the overflow list and left to a second, small launch of the full
+// routine below.  The main kernel then carries one copy of the flat routine and nothing else
+// (it was 190 KB of SASS with the retry and the generic fallback inlined; instruction fetch was
+// 14 % of its stall cycles).  !DEFER: the full routine -- flat, then the generic per-branch code,
+// then a rerun with a global scratch slot -- all decisions depend on the site's data only, so a
+// site gets the same result whichever launch takes it.
+template <int MAXN, int MAXJ, bool HALO, bool DEFER>
+__device__ __forceinline__ void
+mh_update_group(const PassArgs &a, const ModelParams &s_mp, const CtxTables &s_tb,
+                unsigned long long *s_dyn, uint64_t g) {
   const int t = threadIdx.x, lane = t & 31;
   const int n_br = a.tree.n_nodes - 1;
-  if (t == 0) s_mp = a.mp;
-  fill_tables(a.mp, s_tb, t);
-  __syncthreads();
-  const uint64_t gi = (uint64_t)blockIdx.x*MH_THREADS + t;
-  const uint64_t g = gi >= a.g_count ? a.n_groups                // group of sites 3g..3g+2
-                                     : a.g_first + gi + (gi >= a.g_split ? a.g_skip : 0);
   const uint64_t st = 3*g + a.colour;                          // the group's target site
   const int64_t gsite = a.global0 + (int64_t)st;
 
@@ -68,35 +77,45 @@ mh_update_kernel(const PassArgs a) {
   uint8_t pend[MAXN];
   Proposal pr; pr.pj = pj_local; pr.cap = MAXJ; pr.pn = pn; pr.pend = pend;
   int accepted = 0, total = 0;
+  bool deferred = false;
   {
-    const bool active = st >= a.upd_lo && st < a.upd_hi && gsite >= 1 && gsite + 1 < (int64_t)a.n_global;
+    const bool active = g < a.n_groups && st >= a.upd_lo && st < a.upd_hi && gsite >= 1 &&
+                        gsite + 1 < (int64_t)a.n_global;
     SiteCtx c; c.pv = a.in; c.state = a.state; c.W = a.W; c.tree = a.tree; c.site = st;
     int r = mh_site_flat<MAXN, PB, QCAP, HALO>(active, a.coop != 0, s_mp, s_tb, c, a.state, a.tri_llh, a.seed, a.sweep,
                                          (uint64_t)gsite, a.n_global, S, pr, total);
-    // -3: interval stack too small -- a property of the neighbours' rows only, so switching
-    // to the generic per-branch routine here is unbiased (rare; runs divergently)
-    const bool generic = r == -3;
-    if (generic)
-      r = mh_site(s_mp, c, a.state, a.tri_llh, a.seed, a.sweep, (uint64_t)gsite, a.n_global,
-                  S.q, pr, total);
-    // -1: proposal longer than the per-thread buffer: rerun with a global scratch slot and
-    // the same streams (=> the same proposal).  The flat routine is warp-synchronous, so the
-    // whole warp re-enters it with only the overflowing lanes active.
-    if (__any_sync(0xffffffffu, r == -1)) {
-      const bool again = r == -1;
-      if (again) {
-        const uint32_t slot = atomicAdd(a.scratch_ctr, 1u);
-        if (slot >= a.scratch_slots) { atomicOr(a.err, ERR_SCRATCH_SLOTS); r = 0; }
-        else { pr.pj = a.scratch + (uint64_t)slot*a.scratch_cap; pr.cap = (int)a.scratch_cap; }
+    if (DEFER) {
+      if (r == -1 || r == -3) {
+        a.ovf_list[1 + atomicAdd(a.ovf_list, 1u)] = (uint32_t)g;
+        deferred = true; r = 0;
       }
-      const bool redo = again && r == -1;
-      const int r2 = mh_site_flat<MAXN, PB, QCAP, HALO>(redo && !generic, a.coop != 0, s_mp, s_tb, c, a.state, a.tri_llh,
-                                                  a.seed, a.sweep, (uint64_t)gsite, a.n_global, S, pr, total);
-      if (redo && !generic) r = r2;
-      if (redo && generic)
+    }
+    else {
+      // -3: interval stack too small -- a property of the neighbours' rows only, so switching
+      // to the generic per-branch routine here is unbiased (rare; runs divergently)
+      const bool generic = r == -3;
+      if (generic)
         r = mh_site(s_mp, c, a.state, a.tri_llh, a.seed, a.sweep, (uint64_t)gsite, a.n_global,
                     S.q, pr, total);
-      if (r == -1) { atomicOr(a.err, ERR_SCRATCH_SIZE); r = 0; }
+      // -1: proposal longer than the per-thread buffer: rerun with a global scratch slot and
+      // the same streams (=> the same proposal).  The flat routine is warp-synchronous, so the
+      // whole warp re-enters it with only the overflowing lanes active.
+      if (__any_sync(0xffffffffu, r == -1)) {
+        const bool again = r == -1;
+        if (again) {
+          const uint32_t slot = atomicAdd(a.scratch_ctr, 1u);
+          if (slot >= a.scratch_slots) { atomicOr(a.err, ERR_SCRATCH_SLOTS); r = 0; }
+          else { pr.pj = a.scratch + (uint64_t)slot*a.scratch_cap; pr.cap = (int)a.scratch_cap; }
+        }
+        const bool redo = again && r == -1;
+        const int r2 = mh_site_flat<MAXN, PB, QCAP, HALO>(redo && !generic, a.coop != 0, s_mp, s_tb, c, a.state, a.tri_llh,
+                                                    a.seed, a.sweep, (uint64_t)gsite, a.n_global, S, pr, total);
+        if (redo && !generic) r = r2;
+        if (redo && generic)
+          r = mh_site(s_mp, c, a.state, a.tri_llh, a.seed, a.sweep, (uint64_t)gsite, a.n_global,
+                      S.q, pr, total);
+        if (r == -1) { atomicOr(a.err, ERR_SCRATCH_SIZE); r = 0; }
+      }
     }
     if (r == -2) { atomicOr(a.err, ERR_SAMPLER_STUCK); r = 0; }
     if (r < 0) r = 0;
@@ -106,7 +125,7 @@ mh_update_kernel(const PassArgs a) {
   if (lane == 0 && acc_mask) atomicAdd(a.n_accept, (unsigned long long)__popc(acc_mask));
 
   // ---- stage the accepted proposal's rows -----------------------------------------
-  if (g >= a.n_groups) return;
+  if (g >= a.n_groups || deferred) return;
   uint32_t so = STG_REJECTED;
   if (accepted) {
     if (total == 0) so = STG_EMPTY;
@@ -125,6 +144,40 @@ mh_update_kernel(const PassArgs a) {
     }
   }
   a.stage_off[g] = so;
+}
+
+// HALO = false: the main launch (one site per thread, failures deferred).  HALO = true: the full
+// routine on (a) the few groups next to a shard's ends, whose neighbours live in the halo store,
+// and (b) the overflow list of the main launch (a.list_mode; grid-stride over the list, whose
+// length is only known on the device).
+template <int MAXN, int MAXJ, bool HALO, bool DEFER = false>
+__global__ void __launch_bounds__(MH_THREADS, mh_minblocks(MAXN))
+mh_update_kernel(const PassArgs a) {
+  __shared__ ModelParams s_mp;
+  __shared__ CtxTables s_tb;
+  extern __shared__ unsigned long long s_dyn[];    // [MH_THREADS*QCAP] QSlot, then [MH_THREADS] int
+  const int t = threadIdx.x;
+  if (t == 0) s_mp = a.mp;
+  fill_tables(a.mp, s_tb, t);
+  __syncthreads();
+  if (!HALO) {
+    const uint64_t gi = (uint64_t)blockIdx.x*MH_THREADS + t;
+    const uint64_t g = gi >= a.g_count ? a.n_groups                // group of sites 3g..3g+2
+                                       : a.g_first + gi + (gi >= a.g_split ? a.g_skip : 0);
+    mh_update_group<MAXN, MAXJ, false, DEFER>(a, s_mp, s_tb, s_dyn, g);
+  }
+  else {
+    const uint64_t n_items = a.list_mode ? (uint64_t)a.ovf_list[0] : a.g_count;
+    const uint64_t stride = (uint64_t)gridDim.x*MH_THREADS;
+    // (trip count uniform within a warp: the routine is warp-synchronous)
+    for (uint64_t base = (uint64_t)blockIdx.x*MH_THREADS; base + (uint64_t)(t & ~31) < n_items; base += stride) {
+      const uint64_t gi = base + t;
+      uint64_t g = a.n_groups;
+      if (gi < n_items) g = a.list_mode ? (uint64_t)a.ovf_list[1 + gi] : a.g_first + gi + (gi >= a.g_split ? a.g_skip : 0);
+      mh_update_group<MAXN, MAXJ, true, false>(a, s_mp, s_tb, s_dyn, g);
+      __syncwarp();
+    }
+  }
 }
 
 // ---- CSR re-compaction ------------------------------------------------------------------
@@ -304,17 +357,40 @@ static int
 launch_update_t(const PassArgs &a0, cudaStream_t st) {
   const size_t smem = (size_t)MH_THREADS*mh_qcap(MAXN)*sizeof(QSlot) + MH_THREADS*sizeof(int);
   PassArgs a = a0;
+  a.list_mode = 0;
   const uint64_t lo = a.in.own_lo, hi = a.in.own_hi;
   uint64_t g_lo = lo == 0 ? 0 : (lo + 4)/3;                       // first group with 3g - 2 >= own_lo
   uint64_t g_hi = hi == a.in.n_local ? a.n_groups : (hi >= 5 ? (hi - 5)/3 + 1 : 0);   // 3g + 4 < own_hi
   g_lo = g_lo < a.n_groups ? g_lo : a.n_groups;
   g_hi = g_hi > g_lo ? g_hi : g_lo;
   g_hi = g_hi < a.n_groups ? g_hi : a.n_groups;
+  // deferral costs one more launch whose length is the latency of a single site update (~0.1 ms
+  // when a handful of sites overflow): worth it only when the pass is long (1e6-site single branch:
+  // 0.45 vs 0.41 ms per pass with it)
+  // (EPIEVO_B200_DEFER_MIN overrides the threshold: the tests run both ways on small inputs)
+  const char *env = getenv("EPIEVO_B200_DEFER_MIN");
+  const uint64_t defer_min = env ? strtoull(env, nullptr, 10) : (1ull << 20);
+  const bool defer = mh_defer(MAXN) && g_hi - g_lo >= defer_min;
   if (g_hi > g_lo) {
     a.g_first = g_lo; a.g_count = a.g_split = g_hi - g_lo; a.g_skip = 0;
     const unsigned blocks = (unsigned)((a.g_count + MH_THREADS - 1)/MH_THREADS);
-    cudaFuncSetAttribute(mh_update_kernel<MAXN, MAXJ, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    mh_update_kernel<MAXN, MAXJ, false><<<blocks, MH_THREADS, smem, st>>>(a);
+    if (defer) {
+      cudaFuncSetAttribute(mh_update_kernel<MAXN, MAXJ, false, mh_defer(MAXN)>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      mh_update_kernel<MAXN, MAXJ, false, mh_defer(MAXN)><<<blocks, MH_THREADS, smem, st>>>(a);
+    }
+    else {
+      cudaFuncSetAttribute(mh_update_kernel<MAXN, MAXJ, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      mh_update_kernel<MAXN, MAXJ, false, false><<<blocks, MH_THREADS, smem, st>>>(a);
+    }
+  }
+  int launches = (g_hi > g_lo);
+  if (g_hi > g_lo && defer) {
+    // the sites the main launch deferred (list length known on the device only)
+    a.list_mode = 1;
+    cudaFuncSetAttribute(mh_update_kernel<MAXN, MAXJ, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    mh_update_kernel<MAXN, MAXJ, true><<<MH_OVF_BLOCKS, MH_THREADS, smem, st>>>(a);
+    a.list_mode = 0;
+    ++launches;
   }
   const uint64_t n_edge = g_lo + (a.n_groups - g_hi);
   if (n_edge) {
@@ -322,8 +398,9 @@ launch_update_t(const PassArgs &a0, cudaStream_t st) {
     const unsigned blocks = (unsigned)((n_edge + MH_THREADS - 1)/MH_THREADS);
     cudaFuncSetAttribute(mh_update_kernel<MAXN, MAXJ, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     mh_update_kernel<MAXN, MAXJ, true><<<blocks, MH_THREADS, smem, st>>>(a);
+    ++launches;
   }
-  return (g_hi > g_lo) + (n_edge != 0);
+  return launches;
 }
 
 int

@@ -84,3 +84,29 @@ def test_end_cond_sampler_matches_analytic_expectations(ctx, cpu):
             for got, want in ((d0, D0[2*a + b]), (j0, J0[2*a + b]), (j1, J1[2*a + b])):
                 se = got.std()/np.sqrt(n) + 1e-12
                 assert abs(got.mean() - want) < 5*se, (a, b, got.mean(), want, se)
+
+
+@pytest.mark.parametrize("case,n,density", [("testtree", 3000, 1.0), ("testtree", 600, 25.0), ("bal8", 1500, 6.0),
+                                            ("pair", 2000, 8.0)])
+def test_deferred_overflow_launch_gives_the_same_chain(model, case, n, density, monkeypatch):
+    """Long passes defer the sites the flat routine cannot finish (proposal or interval stack too
+    large) to a second launch of the full routine (kernels_mh.cu, mh_update_group); a site's result
+    depends on its data only, so the chain must be bit-identical either way.  The dense cases make
+    many sites overflow."""
+    from epievo_b200.device import Context
+    tree = {"testtree": ref_test_tree, "pair": lambda: Tree.pair(1.0),
+            "bal8": lambda: Tree.balanced(8, 0.05)}[case]()
+    ps = synth_paths(tree, n, 5, density)
+    out = []
+    for defer_min in ("0", "1000000000000"):
+        monkeypatch.setenv("EPIEVO_B200_DEFER_MIN", defer_min)
+        c = Context(0)
+        try:
+            c.set_tree(tree); c.set_model(*model); c.upload_paths(ps); c.reset()
+            J, D, acc = c.run_mcmc(2, 2, seed=9)
+            out.append((J, D, acc, c.download_paths(), c.tri_llh()))
+        finally:
+            c.close()
+    a, b = out
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and a[2] == b[2]
+    assert a[3].same_as(b[3]) and np.array_equal(a[4], b[4])
