@@ -53,3 +53,40 @@ def test_sharded_equals_single(model, case, n, world):
         loc = S.local_paths(want, n, world, s.rank)
         assert parts[s.rank].same_as(loc)
         s.ctx.close()
+
+
+def test_sharded_with_deferred_overflow_launch(model, monkeypatch):
+    """Long passes of a sharded context run three update launches (main with deferral, overflow
+    list, halo-aware edge groups); forced on here through EPIEVO_B200_DEFER_MIN, two shards with
+    dense rows must still reproduce the unsharded chain without deferral."""
+    import torch
+    tree = ref_test_tree()
+    rates, T = model
+    n, world = 900, 2
+    from synth import synth_paths
+    ps = synth_paths(tree, n, 21, 12.0)
+    dev = torch.device("cuda", 0)
+    st = torch.cuda.Stream()
+    torch.cuda.set_stream(st)
+    monkeypatch.setenv("EPIEVO_B200_DEFER_MIN", "1000000000000")
+    one = Context(0)
+    one.set_tree(tree); one.set_model(rates, T); one.upload_paths(ps); one.reset()
+    J1, D1, acc1 = one.run_mcmc(2, 2, seed=13)
+    want = one.download_paths()
+    one.close()
+    monkeypatch.setenv("EPIEVO_B200_DEFER_MIN", "0")
+    shards = []
+    for r in range(world):
+        c = Context(0)
+        c.set_stream(st.cuda_stream)
+        c.set_tree(tree); c.set_model(rates, T)
+        sh = S.Shard(c, n, world, r, dev)
+        c.upload_paths(S.local_paths(ps, n, world, r)); c.reset()
+        shards.append(sh)
+    J, D, acc = S.run_mcmc(shards, S.LocalExchange(shards), 2, 2, seed=13)
+    torch.cuda.synchronize()
+    got = S.gather_paths([s.ctx.download_paths() for s in shards], n, world)
+    for s in shards:
+        s.ctx.close()
+    assert got.same_as(want)
+    assert np.array_equal(J, J1) and np.allclose(D, D1, rtol=1e-12, atol=0) and acc == acc1
