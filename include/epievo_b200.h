@@ -111,7 +111,10 @@ int epv_run_mcmc_raw(epv_ctx *ctx, uint64_t burn_in, uint64_t batch, uint64_t se
 
 /* ---- sufficient statistics, likelihood, gradient -------------------------------- */
 /* replaces get_sufficient_statistics(paths, J, D) per branch
- * (ParamEstimation.cpp:92-114): J, D are [n_nodes*8], row 0 zero. */
+ * (ParamEstimation.cpp:92-114): J, D are [n_nodes*8], row 0 zero.  J is exact; D is summed in
+ * 64-bit fixed point (quantum tot_time * 2^-40 per term, far inside the 1e-9 parity bound),
+ * which makes the result independent of the order in which thread blocks finish: two contexts
+ * holding the same paths return bit-identical D. */
 int epv_suffstats(epv_ctx *ctx, double *J, double *D);
 /* replaces log_likelihood + get_gradient (ParamEstimation.cpp:131-194) evaluated on
  * the device-resident J/D of the last epv_suffstats / epv_run_mcmc, collapsed over
