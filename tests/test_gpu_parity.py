@@ -66,3 +66,22 @@ def test_scale_jump_times(ctx, cpu, model):
     ctx.scale_jump_times(nb)
     cpu.load_paths(ps); cpu.scale_jump_times(nb)
     assert ctx.download_paths().same_as(cpu.store_paths())       # one multiply: bit-exact
+
+
+@pytest.mark.parametrize("case,n,levels,p", [("testtree", 1500, 6, 0.25), ("testtree", 700, 3, 0.6),
+                                             ("pair", 2000, 4, 0.5), ("bal8", 600, 5, 0.15)])
+def test_suffstats_with_tied_jump_times(ctx, cpu, model, case, n, levels, p):
+    """Jump times on a coarse grid: neighbouring rows hold exactly equal times all the time, which
+    pins the tie rule of the J/D kernels (the higher site jumps first, Path.cpp:275-281)."""
+    from test_jd_identity_cpu import grid_paths
+    tree = {"testtree": ref_test_tree, "pair": lambda: Tree.pair(1.0),
+            "bal8": lambda: Tree.balanced(8, 0.05)}[case]()
+    ps = grid_paths(tree, n, 23, levels, p)
+    ctx.set_tree(tree); ctx.set_model(*model); ctx.upload_paths(ps)
+    cpu.load_paths(ps)
+    Jr, Dr = cpu.get_suff_stats()
+    J, D = ctx.suffstats()
+    assert np.array_equal(J, Jr)
+    assert rel_close(D, Dr, 1e-9)
+    ctx.reset()
+    assert rel_close(ctx.tri_llh(), cpu.tri_llh(*model), 1e-9, atol=1e-12)
