@@ -86,6 +86,41 @@ def test_end_cond_sampler_matches_analytic_expectations(ctx, cpu):
                 assert abs(got.mean() - want) < 5*se, (a, b, got.mean(), want, se)
 
 
+def _end_cond_moments(nj, j, a, T, cap):
+    """Per draw: time spent in state 0, jumps out of 0, jumps out of 1."""
+    n = nj.shape[0]
+    k = np.arange(cap)[None, :]
+    t = np.where(k < nj[:, None], j, T)
+    seg = np.diff(np.concatenate([np.zeros((n, 1)), t, np.full((n, 1), T)], axis=1), axis=1)
+    even = (np.arange(seg.shape[1]) % 2 == 0)[None, :]
+    time_a = (seg*even).sum(1)
+    d0 = time_a if a == 0 else T - time_a
+    from_a, from_b = (nj + 1)//2, nj//2
+    return d0, (from_a if a == 0 else from_b), (from_b if a == 0 else from_a)
+
+
+@pytest.mark.parametrize("r0,r1", [(0.09, 10.2), (10.2, 0.09), (0.5, 0.5), (3.0, 0.3), (10.2, 10.2), (0.09, 0.09)])
+@pytest.mark.parametrize("T", [0.01, 0.05, 0.1, 1.0])
+def test_end_cond_sampler_parameter_sweep(ctx, cpu, r0, r1, T):
+    """The same known answers over the context rates the model actually produces (0.09-10.2 with
+    test.param) and over production interval lengths (0.01-0.1) as well as T = 1: E[J0], E[J1], E[D0]
+    given both end states (expectation_J / expectation_D, ContinuousTimeMarkovModel.cpp:167-226).
+    z-test at 5 sigma per statistic (288 statistics over the sweep: family-wise 1.7e-4)."""
+    n, cap = 200000, 64
+    J0, J1, D0, D1 = cpu.expectations(r0, r1, T)
+    for a in (0, 1):
+        for b in (0, 1):
+            nj, j = ctx.end_cond_sample(r0, r1, a, b, T, 1234 + 2*a + b, n, cap=cap)
+            assert nj.max() < cap and np.all((nj & 1) == (a != b))
+            jj = np.where(np.arange(cap)[None, :] < nj[:, None], j, np.inf)
+            assert np.all(np.diff(np.concatenate([np.zeros((n, 1)), jj], 1), axis=1)[np.isfinite(jj)] > 0)
+            assert np.all(j[np.arange(cap)[None, :] < nj[:, None]] < T)
+            d0, j0, j1 = _end_cond_moments(nj, j, a, T, cap)
+            for name, got, want in (("D0", d0, D0[2*a + b]), ("J0", j0, J0[2*a + b]), ("J1", j1, J1[2*a + b])):
+                se = max(got.std()/np.sqrt(n), 1.0/n)     # (rare events: never below one draw's worth)
+                assert abs(got.mean() - want) < 5*se + 1e-12, (r0, r1, T, a, b, name, got.mean(), want, se)
+
+
 @pytest.mark.parametrize("case,n,density", [("testtree", 3000, 1.0), ("testtree", 600, 25.0), ("bal8", 1500, 6.0),
                                             ("pair", 2000, 8.0)])
 def test_deferred_overflow_launch_gives_the_same_chain(model, case, n, density, monkeypatch):
