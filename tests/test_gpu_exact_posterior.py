@@ -50,3 +50,30 @@ def test_dropin_harness_matches_exact_posterior(tmp_path):
         pytest.skip("integration/_build not built")
     _, _, exact, chain = ep.run_harness(ep.B200_MCMC_TEST, 8, 1.0, 4000, 10, 7, str(tmp_path / "b200"))
     ep.assert_same_law(exact, chain, "MCMC_test_b200 n=8 T=1")
+
+
+# ---- trees: exact draws from tests/exact_tree.py (pinned to the reference harness on one branch) ------
+import exact_tree as et
+from test_exact_posterior_cpu import compare_tree, cpu_chain, tree_case
+
+
+@pytest.mark.parametrize("name,n,seed", [("testtree_x5", 6, 6), ("testtree_x5", 6, 4), ("cherry", 7, 4)])
+def test_gpu_sampler_matches_exact_posterior_on_a_tree(ctx, cpu, model, name, n, seed):
+    """Internal nodes, several children, per-branch statistics: 2e4 exact whole-tree draws (forward
+    simulation along every branch + rejection on all leaf sequences) vs 2e4 draws of the GPU sampler,
+    chi-square / KS on J_t / D_t of every branch, family-wise alpha = 1e-3; the reference's CPU sampler
+    through the same test for attribution."""
+    tree, root, leaves = tree_case(name, n, model, seed)
+    rates, T = model
+    exact, acc = et.exact_draws(tree, root, leaves, rates, N_DRAWS, seed=100 + seed)
+    ps = et.initial_paths(tree, root, leaves, seed)
+    ctx.set_tree(tree); ctx.set_model(rates, T); ctx.upload_paths(ps); ctx.reset()
+    chain = np.zeros((N_DRAWS, tree.n_nodes, 16))
+    sweep = 0
+    for k in range(N_DRAWS):
+        J, D, _ = ctx.run_mcmc(THIN, 1, seed=4242 + seed, first_sweep=sweep)
+        sweep += THIN + 1
+        chain[k, :, :8] = J; chain[k, :, 8:] = D
+    p_ref = compare_tree(exact, cpu_chain(cpu, tree, model, ps, N_DRAWS, THIN, 77), "reference sampler on " + name)
+    p = compare_tree(exact, chain, "GPU sampler on %s (reference sampler's smallest p: %.3g)" % (name, p_ref))
+    print("%s seed %d: exact-sampler acceptance %.3g; smallest p: gpu %.3g, reference %.3g" % (name, seed, acc, p, p_ref))

@@ -78,6 +78,8 @@ def main():
         gpu.append(np.concatenate([J[1:].ravel(), D[1:].ravel()]))
     gpu = np.array(gpu)
     R = a.R
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    np.savez_compressed(os.path.join(ROOT, "gpurun_out", "stats_probe_gpu_%s_n%d_R%d_burn%d.npz" % (a.case, a.n, R, a.burn)), gpu=gpu)
     z = (ref.mean(0) - gpu.mean(0))/np.sqrt(ref.var(0, ddof=1)/R + gpu.var(0, ddof=1)/R + 1e-300)
     print("case %s n=%d R=%d burn-in %d batch %d" % (a.case, a.n, R, a.burn, BATCH))
     for i in np.argsort(-np.abs(z))[:12]:
@@ -92,6 +94,14 @@ def main():
     k_eff = C.shape[0]**2/np.sum(C**2)
     print("mean z^2 = %.4f over %d entries (max |z| %.2f); effective independent entries %.1f => null sd of mean z^2 = %.3f"
           % (np.nanmean(z**2), z.size, np.abs(z).max(), k_eff, np.sqrt(2.0/k_eff)))
+    # aggregated statistics (far more power than any single entry): jumps per sweep, overall and per branch
+    k = ref.shape[1]//2
+    def welch(x, y):
+        return (x.mean() - y.mean())/np.sqrt(x.var(ddof=1)/len(x) + y.var(ddof=1)/len(y))
+    print("total J per sweep: ref %.4f gpu %.4f  z=%.2f" % (ref[:, :k].sum(1).mean(), gpu[:, :k].sum(1).mean(),
+                                                             welch(ref[:, :k].sum(1), gpu[:, :k].sum(1))))
+    zb = [welch(ref[:, 8*b:8*b + 8].sum(1), gpu[:, 8*b:8*b + 8].sum(1)) for b in range(k//8)]
+    print("per-branch total J, Welch z:", " ".join("%.2f" % x for x in zb))
     print("CPU half vs CPU half (same law by construction, R/2 each): mean z^2 = %.4f" % np.nanmean(zz**2))
 
 
