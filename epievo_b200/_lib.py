@@ -50,6 +50,32 @@ SIGNATURES = {
     "epv_halo_record_bytes": (C.c_int, [ctx_p, u64p]),
     "epv_halo_pack": (C.c_int, [ctx_p, C.c_int, C.c_void_p, C.c_void_p]),
     "epv_halo_unpack": (C.c_int, [ctx_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "epv_halo_capacity": (C.c_int, [ctx_p, u64p, u64p]),
+    "epv_halo_set_capacity": (C.c_int, [ctx_p, u64]),
+    "epv_set_side_stream": (C.c_int, [ctx_p, C.c_void_p]),
+    "epv_pass_begin": (C.c_int, [ctx_p, C.c_int, u64, u64, C.c_void_p, C.c_void_p]),
+    "epv_pass_end": (C.c_int, [ctx_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "epv_suffstats_async": (C.c_int, [ctx_p]),
+    "epv_suffstats_fetch": (C.c_int, [ctx_p, dp, dp]),
+    "epv_multi_create": (C.c_int, [C.POINTER(ctx_p), C.c_int, C.POINTER(C.c_int)]),
+    "epv_multi_destroy": (None, [ctx_p]),
+    "epv_multi_last_error": (C.c_char_p, [ctx_p]),
+    "epv_multi_shards": (C.c_int, [ctx_p]),
+    "epv_multi_context": (ctx_p, [ctx_p, C.c_int]),
+    "epv_multi_partition": (C.c_int, [u64, C.c_int, u64p, u64p]),
+    "epv_multi_set_tree": (C.c_int, [ctx_p, u64, u64p, u64p, dp]),
+    "epv_multi_set_model": (C.c_int, [ctx_p, dp, dp]),
+    "epv_multi_upload_paths": (C.c_int, [ctx_p, u64, u64, u8p, u64p, dp, dp]),
+    "epv_multi_paths_size": (C.c_int, [ctx_p, u64p, u64p, u64p]),
+    "epv_multi_download_paths": (C.c_int, [ctx_p, u8p, u64p, dp, dp]),
+    "epv_multi_reset": (C.c_int, [ctx_p]),
+    "epv_multi_sweep": (C.c_int, [ctx_p, u64, u64, u64p]),
+    "epv_multi_run_mcmc": (C.c_int, [ctx_p, u64, u64, u64, u64, dp, dp, dp]),
+    "epv_multi_suffstats": (C.c_int, [ctx_p, dp, dp]),
+    "epv_multi_scale_jump_times": (C.c_int, [ctx_p, dp]),
+    "epv_multi_mcem_iteration": (C.c_int, [ctx_p, u64, u64, u64, u64, C.c_int, C.c_double, dp, dp, dp, dp,
+                                           dp, dp]),
+    "epv_multi_launch_count": (u64, [ctx_p]),
     "epv_site_debug": (C.c_int, [ctx_p, u64, u64, u64p, u64p, dp, dp, u64p, u64p, dp, dp, dp,
                                  dp, dp]),
     "epv_get_tri_llh": (C.c_int, [ctx_p, dp]),

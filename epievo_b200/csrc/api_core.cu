@@ -22,6 +22,7 @@ void free_paths(epv_ctx *c) {
   }
   cudaFree(c->d_jbase); cudaFree(c->d_jcap); cudaFree(c->d_state); cudaFree(c->d_tri);
   cudaFree(c->d_desc); cudaFree(c->d_hcnt); cudaFree(c->d_hjmp);
+  c->halo_k = HALO_K_MIN;
   cudaFree(c->d_stage_init); cudaFree(c->d_stage_off); cudaFree(c->d_stg_off); cudaFree(c->d_stg);
   cudaFree(c->d_ovf_list); c->d_ovf_list = nullptr;
   c->d_stg_off = nullptr; c->d_stg = nullptr;
@@ -69,6 +70,11 @@ int epv_create(epv_ctx **out, int device) {
     && cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) == cudaSuccess
     && cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device) == cudaSuccess
     && cudaMalloc(&c->d_err, sizeof(unsigned)) == cudaSuccess
+    && cudaMalloc(&c->d_hmax, sizeof(unsigned)) == cudaSuccess
+    && cudaStreamCreateWithFlags(&c->own_side, cudaStreamNonBlocking) == cudaSuccess
+    && cudaEventCreateWithFlags(&c->ev_begin, cudaEventDisableTiming) == cudaSuccess
+    && cudaEventCreateWithFlags(&c->ev_edge, cudaEventDisableTiming) == cudaSuccess
+    && cudaEventCreateWithFlags(&c->ev_halo, cudaEventDisableTiming) == cudaSuccess
     && cudaMalloc(&c->d_nacc, sizeof(unsigned long long)) == cudaSuccess
     && cudaMalloc(&c->d_ticket, sizeof(uint32_t)) == cudaSuccess
     && cudaMalloc(&c->d_scratch_ctr, sizeof(uint32_t)) == cudaSuccess
@@ -82,7 +88,9 @@ int epv_create(epv_ctx **out, int device) {
     ok = cudaEventCreate(&c->ev_ring[k]) == cudaSuccess;
   if (ok) {
     c->stream = c->own_stream;
+    c->side_stream = c->own_side;
     cudaMemset(c->d_err, 0, sizeof(unsigned));
+    cudaMemset(c->d_hmax, 0, sizeof(unsigned));
     cudaMemset(c->d_nacc, 0, sizeof(unsigned long long));
     cudaMemset(c->d_ticket, 0, sizeof(uint32_t));
     cudaMemset(c->d_scratch_ctr, 0, sizeof(uint32_t));
@@ -103,6 +111,10 @@ void epv_destroy(epv_ctx *c) {
   free_paths(c);
   sim_release(c);
   cudaFree(c->d_parent); cudaFree(c->d_subtree); cudaFree(c->d_branch);
+  cudaStreamSynchronize(c->side_stream);
+  cudaEventDestroy(c->ev_begin); cudaEventDestroy(c->ev_edge); cudaEventDestroy(c->ev_halo);
+  cudaStreamDestroy(c->own_side);
+  cudaFree(c->d_hmax);
   cudaFree(c->d_err); cudaFree(c->d_nacc); cudaFree(c->d_ticket); cudaFree(c->d_scratch_ctr);
   cudaFree(c->d_stg_ctr); cudaFree(c->d_itab); cudaFree(c->d_iacc);
   cudaFree(c->d_scratch); cudaFree(c->d_out9); cudaFree(c->d_mail); cudaFreeHost(c->h_mail);
@@ -125,6 +137,14 @@ int epv_set_stream(epv_ctx *c, void *s) {
 int epv_synchronize(epv_ctx *c) {
   if (!c) return 1;
   EPV_CUDA(c, cudaStreamSynchronize(c->stream));
+  EPV_CUDA(c, cudaStreamSynchronize(c->side_stream));
+  return 0;
+}
+
+int epv_set_side_stream(epv_ctx *c, void *s) {
+  if (!c) return 1;
+  cudaStreamSynchronize(c->side_stream);
+  c->side_stream = s ? (cudaStream_t)s : c->own_side;
   return 0;
 }
 

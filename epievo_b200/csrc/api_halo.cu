@@ -1,4 +1,6 @@
 // api_halo.cu -- C-ABI of the per-colour halo exchange (multi-GPU site sharding).
+#include <algorithm>
+
 #include "../../include/epievo_b200.h"
 #include "context.h"
 
@@ -11,7 +13,8 @@ HaloArgs halo_args(epv_ctx *c) {
   a.pv = c->view(c->cur);
   a.state = c->d_state; a.W = c->W; a.tri_llh = c->d_tri;
   a.n_sites = c->n_sites; a.global0 = c->global0();
-  a.hcnt = c->d_hcnt; a.hjmp = c->d_hjmp; a.err = c->d_err;
+  a.hcnt = c->d_hcnt; a.hjmp = c->d_hjmp; a.err = c->d_err; a.hmax = c->d_hmax;
+  a.stage_off = c->d_stg_off; a.stage = c->d_stg;
   return a;
 }
 
@@ -30,8 +33,30 @@ extern "C" {
 int epv_halo_record_bytes(epv_ctx *c, uint64_t *bytes) {
   if (!c) return 1;
   if (!c->n_nodes) return fail(c, "epv_set_tree must be called first");
-  *bytes = halo_record_words(c->n_nodes)*sizeof(unsigned long long);
+  *bytes = halo_record_words(c->n_nodes, c->halo_k)*sizeof(unsigned long long);
   return 0;
+}
+
+int epv_halo_capacity(epv_ctx *c, uint64_t *capacity, uint64_t *needed) {
+  if (!c) return 1;
+  cudaSetDevice(c->device);
+  unsigned hmax = 0;
+  EPV_CUDA(c, cudaMemcpyAsync(c->h_mail, c->d_hmax, sizeof(unsigned), cudaMemcpyDeviceToHost, c->stream));
+  EPV_CUDA(c, cudaStreamSynchronize(c->stream));
+  hmax = *reinterpret_cast<unsigned *>(c->h_mail);
+  if (capacity) *capacity = (uint64_t)c->halo_k;
+  // regrow while there is still a factor of two of headroom
+  if (needed) *needed = std::max<uint64_t>((uint64_t)c->halo_k, 2*(uint64_t)hmax > (uint64_t)c->halo_k ? 4*(uint64_t)hmax + 16 : 0);
+  return 0;
+}
+
+int epv_halo_set_capacity(epv_ctx *c, uint64_t capacity) {
+  if (!c) return 1;
+  if (!c->n_sites) return fail(c, "no paths loaded");
+  if (capacity > 65000) return fail(c, "halo rows hold at most 65000 jumps");
+  cudaSetDevice(c->device);
+  EPV_CUDA(c, cudaStreamSynchronize(c->stream));
+  return set_halo_capacity(c, (int)capacity);
 }
 
 int epv_halo_pack(epv_ctx *c, int colour, void *rec_lo, void *rec_hi) {

@@ -13,10 +13,9 @@ namespace epv {
 int read_branch_totals(epv_ctx *c, std::vector<uint64_t> &tot) {
   const int n_br = c->n_nodes - 1;
   tot.assign(n_br, 0);
-  for (int bi = 0; bi < n_br; ++bi)
-    EPV_CUDA(c, cudaMemcpyAsync(reinterpret_cast<uint32_t *>(c->h_mail) + bi,
-                                c->d_off[c->cur] + (uint64_t)bi*c->off_pitch + c->n_own(),
-                                sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+  // one strided copy: the closing offset of every branch
+  EPV_CUDA(c, cudaMemcpy2DAsync(c->h_mail, sizeof(uint32_t), c->d_off[c->cur] + c->n_own(), c->off_pitch*sizeof(uint32_t),
+                                sizeof(uint32_t), (size_t)n_br, cudaMemcpyDeviceToHost, c->stream));
   EPV_CUDA(c, cudaStreamSynchronize(c->stream));
   uint64_t sum = 0;
   for (int bi = 0; bi < n_br; ++bi) sum += tot[bi] = reinterpret_cast<uint32_t *>(c->h_mail)[bi];
@@ -87,13 +86,36 @@ int maybe_regrow(epv_ctx *c, const std::vector<uint64_t> &tot) {
 
 namespace epv {
 
-// Host copy of the halo store: counts [2*HALO_W][n_br] and jumps [..][HALO_K].
+// Host copy of the halo store: counts [2*HALO_W][n_br] and jumps [..][halo_k].
 int read_halo_store(epv_ctx *c, std::vector<uint16_t> &cnt, std::vector<double> &jmp) {
   const size_t n_br = c->n_nodes - 1, rows = 2*HALO_W*n_br;
-  cnt.assign(rows, 0); jmp.assign(rows*HALO_K, 0.0);
+  cnt.assign(rows, 0); jmp.assign(rows*c->halo_k, 0.0);
   EPV_CUDA(c, cudaMemcpyAsync(cnt.data(), c->d_hcnt, rows*sizeof(uint16_t), cudaMemcpyDeviceToHost, c->stream));
-  EPV_CUDA(c, cudaMemcpyAsync(jmp.data(), c->d_hjmp, rows*HALO_K*sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  EPV_CUDA(c, cudaMemcpyAsync(jmp.data(), c->d_hjmp, rows*c->halo_k*sizeof(double), cudaMemcpyDeviceToHost, c->stream));
   EPV_CUDA(c, cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+// Halo rows hold up to k jumps each from now on (k only grows); the store's contents are kept.
+int set_halo_capacity(epv_ctx *c, int k) {
+  k = (k + 7) & ~7;
+  if (k <= c->halo_k && c->d_hjmp) return 0;
+  if (k < c->halo_k) k = c->halo_k;
+  const size_t n_br = c->n_nodes - 1, rows = 2*HALO_W*n_br;
+  std::vector<uint16_t> cnt; std::vector<double> old;
+  const int k_old = c->halo_k;
+  if (c->d_hjmp) {
+    if (c->side_stream) EPV_CUDA(c, cudaStreamSynchronize(c->side_stream));
+    if (int r = read_halo_store(c, cnt, old)) return r;
+    cudaFree(c->d_hjmp); c->d_hjmp = nullptr;
+  }
+  EPV_CUDA(c, cudaMalloc(&c->d_hjmp, rows*k*sizeof(double)));
+  c->halo_k = k;
+  if (!old.empty()) {
+    std::vector<double> nw(rows*k, 0.0);
+    for (size_t r = 0; r < rows; ++r) std::memcpy(&nw[r*k], &old[r*k_old], (size_t)cnt[r]*sizeof(double));
+    EPV_CUDA(c, cudaMemcpy(c->d_hjmp, nw.data(), nw.size()*sizeof(double), cudaMemcpyHostToDevice));
+  }
   return 0;
 }
 
@@ -122,6 +144,9 @@ static int check_upload(epv_ctx *c, uint64_t n_sites, uint64_t n_nodes, const do
     if (tot_time[b] != c->h_branch[b])
       return fail(c, "paths' tot_time differs from the tree's branch length (the reference "
                      "asserts equality, Segment.cpp:76); rescale the paths or the tree");
+  // new paths: a device-side failure of the previous ones (sticky flags) no longer applies
+  EPV_CUDA(c, cudaMemsetAsync(c->d_err, 0, sizeof(unsigned), c->stream));
+  EPV_CUDA(c, cudaMemsetAsync(c->d_hmax, 0, sizeof(unsigned), c->stream));
   return 0;
 }
 
@@ -146,7 +171,7 @@ static int ensure_shape(epv_ctx *c, uint64_t n_sites) {
   EPV_CUDA(c, cudaMalloc(&c->d_tri, n_sites*sizeof(double)));
   EPV_CUDA(c, cudaMalloc(&c->d_desc, (size_t)n_br*c->n_tiles*sizeof(unsigned long long)));
   EPV_CUDA(c, cudaMalloc(&c->d_hcnt, (size_t)2*HALO_W*n_br*sizeof(uint16_t)));
-  EPV_CUDA(c, cudaMalloc(&c->d_hjmp, (size_t)2*HALO_W*n_br*HALO_K*sizeof(double)));
+  if (int r = set_halo_capacity(c, c->halo_k)) return r;
   const uint64_t n_rows = (uint64_t)c->n_nodes*n_sites;
   EPV_CUDA(c, cudaMalloc(&c->d_stage_init, n_rows));
   EPV_CUDA(c, cudaMalloc(&c->d_stage_off, (n_rows + 1)*sizeof(unsigned long long)));
@@ -211,18 +236,29 @@ int epv_upload_paths(epv_ctx *c, uint64_t n_sites, uint64_t n_nodes, const uint8
     if (count[bi])
       EPV_CUDA(c, cudaMemcpyAsync(c->d_jmp[0] + c->h_jbase[bi], jumps + first[bi],
                                   count[bi]*sizeof(double), cudaMemcpyHostToDevice, c->stream));
-  // halo rows -> fixed-capacity halo store
+  // halo rows -> halo store, its row capacity sized from the rows next to the shard's ends
+  if (c->halo_lo || c->halo_hi) {
+    uint64_t kmax = 0;
+    for (int bi = 0; bi < n_br; ++bi)
+      for (uint64_t d = 0; d < 2*HALO_W; ++d) {
+        const uint64_t r = (uint64_t)(bi + 1)*n_sites;
+        if (c->halo_lo) kmax = std::max(kmax, row_off[r + d + 1] - row_off[r + d]);
+        if (c->halo_hi) kmax = std::max(kmax, row_off[r + n_sites - d] - row_off[r + n_sites - d - 1]);
+      }
+    if (kmax > 30000) return fail(c, "a shard-boundary row holds more than 30000 jumps");
+    if (int r = set_halo_capacity(c, std::max<int>(HALO_K_MIN, 2*(int)kmax + 16))) return r;
+  }
+  const size_t HK = c->halo_k;
   std::vector<uint16_t> hc((size_t)2*HALO_W*n_br, 0);
-  std::vector<double> hj((size_t)2*HALO_W*n_br*HALO_K, 0.0);
+  std::vector<double> hj((size_t)2*HALO_W*n_br*HK, 0.0);
   for (int k = 0; k < 2*HALO_W; ++k) {
     const int64_t s = slot_site(c, k);
     if (s < 0) continue;
     for (int bi = 0; bi < n_br; ++bi) {
       const uint64_t r = (uint64_t)(bi + 1)*n_sites + (uint64_t)s;
       const uint64_t n = row_off[r + 1] - row_off[r];
-      if (n > HALO_K) return fail(c, "a halo row holds more jumps than the halo store's per-row capacity");
       hc[(size_t)k*n_br + bi] = (uint16_t)n;
-      std::memcpy(&hj[((size_t)k*n_br + bi)*HALO_K], jumps + row_off[r], n*sizeof(double));
+      std::memcpy(&hj[((size_t)k*n_br + bi)*HK], jumps + row_off[r], n*sizeof(double));
     }
   }
   EPV_CUDA(c, cudaMemcpyAsync(c->d_hcnt, hc.data(), hc.size()*sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream));
@@ -257,7 +293,7 @@ static int copy_jumps_out(epv_ctx *c, const std::vector<uint64_t> &own, const st
     for (int k = 0; k < HALO_W; ++k)
       if (slot_site(c, k) >= 0) {
         const size_t row = (size_t)k*n_br + bi;
-        std::memcpy(dst, &hj[row*HALO_K], hc[row]*sizeof(double)); dst += hc[row];
+        std::memcpy(dst, &hj[row*c->halo_k], hc[row]*sizeof(double)); dst += hc[row];
       }
     if (own[bi])
       EPV_CUDA(c, cudaMemcpyAsync(dst, c->d_jmp[c->cur] + c->h_jbase[bi], own[bi]*sizeof(double),
@@ -266,7 +302,7 @@ static int copy_jumps_out(epv_ctx *c, const std::vector<uint64_t> &own, const st
     for (int k = HALO_W; k < 2*HALO_W; ++k)
       if (slot_site(c, k) >= 0) {
         const size_t row = (size_t)k*n_br + bi;
-        std::memcpy(dst, &hj[row*HALO_K], hc[row]*sizeof(double)); dst += hc[row];
+        std::memcpy(dst, &hj[row*c->halo_k], hc[row]*sizeof(double)); dst += hc[row];
       }
   }
   return 0;
@@ -362,8 +398,21 @@ int epv_upload_paths_compact(epv_ctx *c, uint64_t n_sites, uint64_t n_nodes, con
       EPV_CUDA(c, cudaMemcpyAsync(c->d_jmp[0] + c->h_jbase[bi], jumps + first[bi],
                                   count[bi]*sizeof(double), cudaMemcpyHostToDevice, c->stream));
   // halo sites (at most 2*HALO_W): state bits and the fixed-capacity halo store, from the host
+  if (c->halo_lo || c->halo_hi) {
+    uint64_t kmax = 0;
+    for (int bi = 0; bi < n_br; ++bi) {
+      const uint16_t *row = row_code + (uint64_t)(bi + 1)*n_sites;
+      for (uint64_t d = 0; d < 2*HALO_W; ++d) {
+        if (c->halo_lo) kmax = std::max<uint64_t>(kmax, row[d] & 0x7fffu);
+        if (c->halo_hi) kmax = std::max<uint64_t>(kmax, row[n_sites - 1 - d] & 0x7fffu);
+      }
+    }
+    if (kmax > 30000) return fail(c, "a shard-boundary row holds more than 30000 jumps");
+    if (int r = set_halo_capacity(c, std::max<int>(HALO_K_MIN, 2*(int)kmax + 16))) return r;
+  }
+  const size_t HK = c->halo_k;
   std::vector<uint16_t> hc((size_t)2*HALO_W*n_br, 0);
-  std::vector<double> hj((size_t)2*HALO_W*n_br*HALO_K, 0.0);
+  std::vector<double> hj((size_t)2*HALO_W*n_br*HK, 0.0);
   std::vector<uint8_t> hs((size_t)2*HALO_W*c->W, 0);
   for (int bi = -1; bi < n_br; ++bi) {
     const uint16_t *row = row_code + (uint64_t)(bi + 1)*n_sites;
@@ -374,10 +423,9 @@ int epv_upload_paths_compact(epv_ctx *c, uint64_t n_sites, uint64_t n_nodes, con
       if (row[s] >> 15) hs[(size_t)k*c->W + (bi + 1)/8] |= (uint8_t)(1u << ((bi + 1) & 7));
       if (bi < 0) continue;
       const uint64_t n = row[s] & 0x7fffu;
-      if (n > HALO_K) return fail(c, "a halo row holds more jumps than the halo store's per-row capacity");
       uint64_t &pos = k < HALO_W ? lo : hi;
       hc[(size_t)k*n_br + bi] = (uint16_t)n;
-      std::memcpy(&hj[((size_t)k*n_br + bi)*HALO_K], jumps + pos, n*sizeof(double));
+      std::memcpy(&hj[((size_t)k*n_br + bi)*HK], jumps + pos, n*sizeof(double));
       pos += n;
     }
   }

@@ -51,7 +51,11 @@ int do_reset(epv_ctx *c) {
 
 struct IndepLaunch { const IndepTab *tab; double r0, r1; };
 
-int one_pass(epv_ctx *c, int colour, uint64_t seed, uint32_t sweep, const IndepLaunch *indep = nullptr) {
+// split: the halo-aware edge groups run FIRST, on the context's side stream, so that the boundary
+// site's record can be packed (from the staging blob) and sent while the interior groups and the CSR
+// rebuild run on the main stream (epv_pass_begin / epv_pass_end).
+int one_pass(epv_ctx *c, int colour, uint64_t seed, uint32_t sweep, const IndepLaunch *indep = nullptr,
+             bool split = false) {
   if (++c->epoch >= (1u << 30)) {
     EPV_CUDA(c, cudaMemsetAsync(c->d_desc, 0, (size_t)(c->n_nodes - 1)*c->n_tiles*sizeof(unsigned long long), c->stream));
     c->epoch = 1;
@@ -65,6 +69,8 @@ int one_pass(epv_ctx *c, int colour, uint64_t seed, uint32_t sweep, const IndepL
   a.n_sites = c->n_sites; a.upd_lo = c->upd_lo(); a.upd_hi = c->upd_hi();
   a.global0 = c->global0(); a.n_global = c->n_global;
   a.colour = colour; a.seed = seed; a.sweep = sweep;
+  a.q_slots = 0;
+  for (int v = 1; v < c->n_nodes; ++v) a.q_slots += c->h_subtree[v] > 1;
   // sparse rows (0.05 jumps each on the 8-leaf tree): few lanes have jump times to draw, so
   // the warp pools them (5.5 vs 6.5 ms per pass); dense rows (1 jump each on the pairwise
   // branch): every lane is busy anyway and pooling only adds traffic (0.44 vs 0.39 ms)
@@ -86,10 +92,18 @@ int one_pass(epv_ctx *c, int colour, uint64_t seed, uint32_t sweep, const IndepL
   }
   int n_upd = 1;
   if (indep) launch_indep_sample(a, indep->tab, indep->r0, indep->r1, c->stream);
-  else n_upd = launch_mh_pass(a, c->stream);        // 1, or 2 for a sharded context
+  else if (!split) n_upd = launch_mh_pass(a, c->stream);        // 1, or 2 for a sharded context
+  else {
+    EPV_CUDA(c, cudaEventRecord(c->ev_begin, c->stream));        // counters reset, previous rebuild done
+    EPV_CUDA(c, cudaStreamWaitEvent(c->side_stream, c->ev_begin, 0));
+    n_upd = launch_mh_edge(a, c->side_stream);
+    EPV_CUDA(c, cudaEventRecord(c->ev_edge, c->side_stream));
+    n_upd += launch_mh_interior(a, c->stream);
+  }
   if (c->timing) {
     cudaEventRecord(c->ev_ring[3*c->ev_pending + 1], c->stream);
   }
+  if (split) EPV_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_edge, 0));   // the rebuild reads every group's staging
   launch_csr_rebuild(a, c->stream);
   if (c->timing) {
     cudaEventRecord(c->ev_ring[3*c->ev_pending + 2], c->stream);
@@ -110,11 +124,21 @@ int one_sweep(epv_ctx *c, uint64_t seed, uint64_t sweep_idx) {
   return 0;
 }
 
-// After a sweep: surface device-side failures and keep capacity headroom.
+// After a sweep: surface device-side failures and keep capacity headroom.  One strided copy of the
+// branch totals + the error word, one synchronisation.
 int housekeeping(epv_ctx *c) {
-  if (int r = check_device_flags(c)) return r;
-  std::vector<uint64_t> tot;
-  if (int r = read_branch_totals(c, tot)) return r;
+  const int n_br = c->n_nodes - 1;
+  uint32_t *mail = reinterpret_cast<uint32_t *>(c->h_mail);
+  EPV_CUDA(c, cudaMemcpy2DAsync(mail + 1, sizeof(uint32_t), c->d_off[c->cur] + c->n_own(), c->off_pitch*sizeof(uint32_t),
+                                sizeof(uint32_t), (size_t)n_br, cudaMemcpyDeviceToHost, c->stream));
+  EPV_CUDA(c, cudaMemcpyAsync(mail, c->d_err, sizeof(unsigned), cudaMemcpyDeviceToHost, c->stream));
+  EPV_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (c->halo_lo || c->halo_hi) EPV_CUDA(c, cudaStreamSynchronize(c->side_stream));
+  if (mail[0]) return check_device_flags(c);
+  std::vector<uint64_t> tot(n_br);
+  uint64_t sum = 0;
+  for (int bi = 0; bi < n_br; ++bi) sum += tot[bi] = mail[1 + bi];
+  c->jumps_per_row = (double)sum/((double)n_br*(double)c->n_own());
   return maybe_regrow(c, tot);
 }
 
@@ -213,6 +237,26 @@ int epv_suffstats(epv_ctx *c, double *J, double *D) {
   return 0;
 }
 
+/* The J/D pass enqueued only (a multi-GPU driver starts it on every shard before reading any back). */
+int epv_suffstats_async(epv_ctx *c) {
+  if (!c) return 1;
+  if (!c->n_sites) return fail(c, "no paths loaded");
+  cudaSetDevice(c->device);
+  return do_suffstats(c);
+}
+
+int epv_suffstats_fetch(epv_ctx *c, double *J, double *D) {
+  if (!c) return 1;
+  if (!c->stats_valid) return fail(c, "epv_suffstats_fetch needs a preceding epv_suffstats_async on the current paths");
+  cudaSetDevice(c->device);
+  const size_t nb = (size_t)c->n_nodes*8*sizeof(double);
+  EPV_CUDA(c, cudaMemcpyAsync(J, c->d_J, nb, cudaMemcpyDeviceToHost, c->stream));
+  EPV_CUDA(c, cudaMemcpyAsync(D, c->d_D, nb, cudaMemcpyDeviceToHost, c->stream));
+  EPV_CUDA(c, cudaStreamSynchronize(c->stream));
+  EPV_CUDA(c, cudaGetLastError());
+  return 0;
+}
+
 int epv_llh_grad(epv_ctx *c, const double *rates, double *llh, double *grad) {
   if (!c) return 1;
   if (!c->stats_valid) return fail(c, "epv_llh_grad needs a preceding epv_suffstats on the current paths");
@@ -240,7 +284,7 @@ int epv_scale_jump_times(epv_ctx *c, const double *new_branches) {
   double *d_scale = reinterpret_cast<double *>(c->d_mail);
   EPV_CUDA(c, cudaMemcpyAsync(d_scale, scale.data(), c->n_nodes*sizeof(double), cudaMemcpyHostToDevice, c->stream));
   launch_scale_jumps(c->d_jmp[c->cur], c->d_jbase, c->d_off[c->cur], c->off_pitch, c->n_own(),
-                     c->n_nodes - 1, d_scale, c->d_hjmp, c->stream);
+                     c->n_nodes - 1, d_scale, c->d_hjmp, c->halo_k, c->stream);
   c->launches += 2;
   for (int b = 1; b < c->n_nodes; ++b) c->h_branch[b] = new_branches[b];
   EPV_CUDA(c, cudaMemcpyAsync(c->d_branch, c->h_branch.data(), c->n_nodes*sizeof(double), cudaMemcpyHostToDevice, c->stream));
@@ -308,6 +352,78 @@ int epv_pass(epv_ctx *c, int colour, uint64_t seed, uint64_t sweep_idx) {
   if (colour < 0 || colour > 2) return fail(c, "colour must be 0, 1 or 2");
   if (!c->tri_valid) if (int r = do_reset(c)) return r;
   if (int r = one_pass(c, colour, seed, (uint32_t)sweep_idx)) return r;
+  if (colour == 2) if (int r = housekeeping(c)) return r;
+  EPV_CUDA(c, cudaGetLastError());
+  return 0;
+}
+
+// The colour pass of a SHARDED context with the halo traffic overlapped (see one_pass): on return the
+// side stream holds: edge update -> pack of the boundary sites' records into rec_lo / rec_hi; the main
+// stream: interior update -> rebuild.  The driver moves the records on the side stream and calls
+// epv_pass_end with what it received.
+int epv_pass_begin(epv_ctx *c, int colour, uint64_t seed, uint64_t sweep_idx, void *rec_lo, void *rec_hi) {
+  if (int r = ready(c)) return r;
+  if (colour < 0 || colour > 2) return fail(c, "colour must be 0, 1 or 2");
+  if (c->split_open) return fail(c, "epv_pass_begin: the previous pass was not closed with epv_pass_end");
+  if (!c->tri_valid) if (int r = do_reset(c)) return r;
+  if (int r = one_pass(c, colour, seed, (uint32_t)sweep_idx, nullptr, true)) return r;
+  c->split_open = true;
+  if (c->halo_lo || c->halo_hi) {
+    const int64_t own_lo = (int64_t)c->halo_lo, own_hi = (int64_t)(c->n_sites - c->halo_hi);
+    int64_t site_lo = -1, site_hi = -1;
+    if (c->halo_lo) {
+      if (!rec_lo) return fail(c, "epv_pass_begin: this shard has a low neighbour, rec_lo is required");
+      site_lo = own_lo + colour;
+    }
+    if (c->halo_hi) {
+      if (!rec_hi) return fail(c, "epv_pass_begin: this shard has a high neighbour, rec_hi is required");
+      site_hi = own_hi - 3 + (((colour - (own_hi - 3)) % 3) + 3) % 3;
+    }
+    HaloArgs h;
+    h.pv = c->view(c->cur ^ 1);                       // the CSR this pass read (one_pass has flipped cur)
+    h.state = c->d_state; h.W = c->W; h.tri_llh = c->d_tri;
+    h.n_sites = c->n_sites; h.global0 = c->global0();
+    h.hcnt = c->d_hcnt; h.hjmp = c->d_hjmp; h.err = c->d_err; h.hmax = c->d_hmax;
+    h.stage_off = c->d_stg_off; h.stage = c->d_stg;
+    launch_halo_pack(h, site_lo, static_cast<unsigned long long *>(rec_lo), site_hi,
+                     static_cast<unsigned long long *>(rec_hi), c->side_stream, true);
+    ++c->launches;
+  }
+  EPV_CUDA(c, cudaGetLastError());
+  return 0;
+}
+
+// Closes the pass: unpacks the neighbours' records (side stream, after whatever the driver enqueued
+// there) and makes the main stream's next work wait for it.  After colour 2: housekeeping (one host
+// synchronisation per sweep).
+int epv_pass_end(epv_ctx *c, int colour, const void *rec_lo, const void *rec_hi) {
+  if (!c) return 1;
+  if (!c->split_open) return fail(c, "epv_pass_end without epv_pass_begin");
+  cudaSetDevice(c->device);
+  c->split_open = false;
+  if (c->halo_lo || c->halo_hi) {
+    const int64_t own_hi = (int64_t)(c->n_sites - c->halo_hi);
+    int64_t site_lo = -1, site_hi = -1;
+    if (c->halo_lo) {
+      if (!rec_lo) return fail(c, "epv_pass_end: this shard has a low neighbour, rec_lo is required");
+      site_lo = colour;
+    }
+    if (c->halo_hi) {
+      if (!rec_hi) return fail(c, "epv_pass_end: this shard has a high neighbour, rec_hi is required");
+      site_hi = own_hi + (((colour - own_hi) % 3) + 3) % 3;
+    }
+    HaloArgs h;
+    h.pv = c->view(c->cur);
+    h.state = c->d_state; h.W = c->W; h.tri_llh = c->d_tri;
+    h.n_sites = c->n_sites; h.global0 = c->global0();
+    h.hcnt = c->d_hcnt; h.hjmp = c->d_hjmp; h.err = c->d_err; h.hmax = c->d_hmax;
+    h.stage_off = c->d_stg_off; h.stage = c->d_stg;
+    launch_halo_unpack(h, site_lo, static_cast<const unsigned long long *>(rec_lo), site_hi,
+                       static_cast<const unsigned long long *>(rec_hi), c->side_stream);
+    ++c->launches;
+    EPV_CUDA(c, cudaEventRecord(c->ev_halo, c->side_stream));
+    EPV_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_halo, 0));
+  }
   if (colour == 2) if (int r = housekeeping(c)) return r;
   EPV_CUDA(c, cudaGetLastError());
   return 0;

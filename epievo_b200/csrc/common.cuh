@@ -15,7 +15,7 @@ enum : unsigned {
   ERR_SCRATCH_SIZE  = 4u,   // one proposal longer than a scratch slot
   ERR_SAMPLER_STUCK = 8u,   // end-conditioned sampler exceeded its iteration cap
   ERR_BAD_INPUT     = 16u,
-  ERR_HALO_CAPACITY = 32u,  // a boundary row has more than HALO_K jumps
+  ERR_HALO_CAPACITY = 32u,  // a boundary row has more jumps than a halo row holds
   ERR_HALO_MISMATCH = 64u,  // a halo record arrived for another site / colour
   ERR_STAGE_CAPACITY = 128u,// accepted proposals of one pass exceed the staging buffer
 };
@@ -36,10 +36,11 @@ struct ModelParams {
 // index = site - own_lo).  The <= 3 halo sites on either side (copies of the neighbour
 // GPUs' boundary sites, refreshed after every colour pass) are kept in a small
 // fixed-capacity halo store so that a refresh never forces a re-compaction:
-//   hcnt[slot*n_br + bi], hjmp[(slot*n_br + bi)*HALO_K ...], slot = site for the low
+//   hcnt[slot*n_br + bi], hjmp[(slot*n_br + bi)*halo_k ...], slot = site for the low
 //   halo, 3 + (site - own_hi) for the high halo.
 constexpr int HALO_W = 3;        // halo width in sites (dependence radius is 2)
-constexpr int HALO_K = 48;       // jump capacity of one halo row (overflow = loud error)
+constexpr int HALO_K_MIN = 48;   // smallest jump capacity of one halo row; the context's halo_k is sized from
+                                 // the boundary rows at upload and regrown between sweeps (overflow = loud error)
 
 struct PathView {
   const uint32_t *off;
@@ -51,6 +52,7 @@ struct PathView {
   const uint16_t *hcnt;
   const double *hjmp;
   int n_br;
+  int halo_k;               // jump capacity of one halo row
 };
 
 struct TreeDev {

@@ -68,7 +68,13 @@ struct epv_ctx {
 
   // halo store (rows of the <= 3 + 3 halo sites, outside the CSR; see common.cuh)
   uint16_t *d_hcnt = nullptr;               // [2*HALO_W][n_br]
-  double *d_hjmp = nullptr;                 // [2*HALO_W][n_br][HALO_K]
+  double *d_hjmp = nullptr;                 // [2*HALO_W][n_br][halo_k]
+  int halo_k = epv::HALO_K_MIN;             // jump capacity of one halo row (the same on every shard of a run)
+  unsigned *d_hmax = nullptr;               // largest boundary-row jump count seen by the pack kernels
+  // second stream of a sharded context: edge groups + halo traffic overlap the interior update
+  cudaStream_t side_stream = nullptr, own_side = nullptr;
+  cudaEvent_t ev_begin = nullptr, ev_edge = nullptr, ev_halo = nullptr;
+  bool split_open = false;                  // between epv_pass_begin and epv_pass_end
 
   // result of epv_simulate until epv_simulate_fetch (api_sim.cu)
   void *sim = nullptr;
@@ -87,7 +93,7 @@ struct epv_ctx {
   epv::PathView view(int which) const {
     epv::PathView v; v.off = d_off[which]; v.jmp = d_jmp[which]; v.jbase = d_jbase;
     v.off_pitch = off_pitch; v.own_lo = halo_lo; v.own_hi = n_sites - halo_hi; v.n_local = n_sites;
-    v.hcnt = d_hcnt; v.hjmp = d_hjmp; v.n_br = n_nodes - 1; return v;
+    v.hcnt = d_hcnt; v.hjmp = d_hjmp; v.n_br = n_nodes - 1; v.halo_k = halo_k; return v;
   }
   epv::TreeDev tree() const {
     epv::TreeDev t; t.n_nodes = n_nodes; t.parent = d_parent; t.subtree = d_subtree;
@@ -104,6 +110,7 @@ int fail(epv_ctx *c, const std::string &msg);
 int check_cuda(epv_ctx *c, cudaError_t e, const char *what);
 void free_paths(epv_ctx *c);
 int check_device_flags(epv_ctx *c);
+int set_halo_capacity(epv_ctx *c, int k);  // reallocates the halo store (contents kept)
 void sim_release(epv_ctx *c);          // frees what epv_simulate left on the device   // reads d_err, turns sticky flags into an error
 }
 #define EPV_CUDA(c, call) do { if (int _r = epv::check_cuda((c), (call), #call)) return _r; } while (0)

@@ -24,6 +24,7 @@ struct PassArgs {
   int64_t global0;            // global index of local site 0
   uint64_t n_global;
   int colour;
+  int q_slots;                // internal non-root nodes of the tree (q kept in shared memory)
   int coop;                   // warp-cooperative jump-time sampling (pays when jumps are sparse)
   uint64_t seed;
   uint32_t sweep;
@@ -51,7 +52,9 @@ struct PassArgs {
   unsigned long long *n_accept;
 };
 
-int launch_mh_pass(const PassArgs &a, cudaStream_t st);       // update kernel
+int launch_mh_pass(const PassArgs &a, cudaStream_t st);       // update kernel: interior groups, then edge groups
+int launch_mh_interior(const PassArgs &a, cudaStream_t st);   // groups whose sites s-2..s+2 are all owned (+ their overflow launch)
+int launch_mh_edge(const PassArgs &a, cudaStream_t st);       // groups next to a shard's ends (halo-aware)
 void launch_csr_rebuild(const PassArgs &a, cudaStream_t st);   // re-compaction kernel
 size_t mh_pass_smem_bytes(int n_nodes);
 
@@ -84,7 +87,7 @@ void launch_axpy_stats(double *J_sum, double *D_sum, const double *J, const doub
 
 void launch_scale_jumps(double *jmp, const uint64_t *jbase, const uint32_t *off,
                         uint64_t off_pitch, uint64_t n_own, int n_branches,
-                        const double *scale, double *hjmp, cudaStream_t st);
+                        const double *scale, double *hjmp, int halo_k, cudaStream_t st);
 
 // host exchange format <-> device layout
 void launch_import(const uint8_t *h_init, const unsigned long long *h_off,
@@ -115,7 +118,8 @@ void launch_indep_sample(const PassArgs &a, const IndepTab *tab, double r0, doub
 // ---- halo exchange (multi-GPU): one boundary site per side per colour pass -------------
 // Record (8-byte words): [0..2] tri_llh[s-1], [s], [s+1]; [3] global site index;
 // [4 .. 4+SW) state bytes; then n_br u16 jump counts packed in CW words; then
-// n_br*HALO_K jump times.
+// n_br*halo_k jump times (halo_k = pv.halo_k, the same on every shard of a run).
+constexpr uint32_t STG_REJECTED = 0xffffffffu, STG_EMPTY = 0xfffffffeu;   // stage_off markers
 struct HaloArgs {
   PathView pv;
   uint8_t *state; int W;
@@ -123,11 +127,16 @@ struct HaloArgs {
   uint64_t n_sites; int64_t global0;
   uint16_t *hcnt; double *hjmp;        // writable halo store (unpack)
   unsigned *err;
+  unsigned *hmax;                      // largest jump count of a packed boundary row seen so far (atomicMax)
+  // staged variant of the pack: pv is the CSR the colour pass READ; the boundary site's new rows are
+  // taken from the proposal staging blob when its update was accepted (before the CSR is rebuilt)
+  const uint32_t *stage_off;
+  const double *stage;
 };
-size_t halo_record_words(int n_nodes);
+size_t halo_record_words(int n_nodes, int halo_k);
 // site_lo / site_hi: local index of the owned boundary site to pack (or -1: side absent)
 void launch_halo_pack(const HaloArgs &a, int64_t site_lo, unsigned long long *rec_lo,
-                      int64_t site_hi, unsigned long long *rec_hi, cudaStream_t st);
+                      int64_t site_hi, unsigned long long *rec_hi, cudaStream_t st, bool staged = false);
 // site_lo / site_hi: local index of the halo site each record must describe (or -1)
 void launch_halo_unpack(const HaloArgs &a, int64_t site_lo, const unsigned long long *rec_lo,
                         int64_t site_hi, const unsigned long long *rec_hi, cudaStream_t st);

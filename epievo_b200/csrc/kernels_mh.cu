@@ -21,13 +21,13 @@
 
 #include "kernels.h"
 #include "mh_flat.cuh"
+#include "mh_lock.cuh"
 #include "scan.cuh"
 
 namespace epv {
 
 namespace {
 
-constexpr uint32_t STG_REJECTED = 0xffffffffu, STG_EMPTY = 0xfffffffeu;
 constexpr unsigned MH_OVF_BLOCKS = 296;     // grid of the overflow launch (grid-stride over the list)
 
 // The main update launch defers the sites its flat routine cannot finish to a second launch
@@ -46,6 +46,17 @@ __host__ __device__ constexpr int mh_minblocks(int) { return EPV_MH_MINBLOCKS; }
 __host__ __device__ constexpr int mh_minblocks(int maxn) { return maxn <= 16 ? 4 : 3; }
 #endif
 
+// The lockstep routine (mh_lock.cuh: branch loop warp-uniform, table-driven single-interval branches)
+// reproduces the flat routine's chains bit for bit (tests/test_gpu_chain_golden.py) but measured SLOWER
+// on the B200: 6.56 vs 5.12 ms per pass (8-leaf tree), 7.30 vs 5.64 (test tree), 8.48 vs 7.52 (32-leaf
+// tree), 0.44 vs 0.41 (1e6-site single branch) -- the interval loop of the lanes that do have neighbour
+// jumps runs per BRANCH (max over lanes of the branch's intervals, ~2.2 heavy iterations per branch at 2-4
+// active lanes) instead of once per site.  Kept behind EPV_MH_LOCK as the base of the next step.
+#ifndef EPV_MH_LOCK
+#define EPV_MH_LOCK 0
+#endif
+__host__ __device__ constexpr bool mh_lock(int maxn) { return EPV_MH_LOCK && maxn <= 64; }
+
 // jump-queue slots per thread (shared memory: 24 B each)
 __host__ __device__ constexpr int mh_qcap(int maxn) { return maxn <= 16 ? 8 : maxn <= 64 ? 16 : 24; }
 
@@ -58,32 +69,57 @@ __host__ __device__ constexpr int mh_qcap(int maxn) { return maxn <= 16 ? 8 : ma
 // 14 % of its stall cycles).  !DEFER: the full routine -- flat, then the generic per-branch code,
 // then a rerun with a global scratch slot -- all decisions depend on the site's data only, so a
 // site gets the same result whichever launch takes it.
-template <int MAXN, int MAXJ, bool HALO, bool DEFER>
+// Shared memory of the update kernel, in this order: jump queue [MH_THREADS*QCAP] QSlot, prefix counts
+// [MH_THREADS] int, then (lockstep routine, trees up to 64 nodes) TreeTab [n_nodes], BranchTab [n_nodes],
+// jump counts per node u16 [n_nodes][MH_THREADS], q of the internal nodes f64 [2*slots][MH_THREADS].
+struct MhShared {
+  QSlot *queue; int *excl; TreeTab *tt; BranchTab *bt; uint16_t *pn; double *q;
+};
+template <int MAXN>
+__host__ __device__ inline size_t mh_smem_layout(int n_nodes, int q_slots, size_t *off /*[6]*/) {
+  size_t at = 0;
+  off[0] = at; at += (size_t)MH_THREADS*mh_qcap(MAXN)*sizeof(QSlot);
+  off[1] = at; at += (size_t)MH_THREADS*sizeof(int);
+  if (mh_lock(MAXN)) {
+    at = (at + 15) & ~(size_t)15;
+    off[2] = at; at += (size_t)n_nodes*sizeof(TreeTab);
+    off[3] = at; at += (size_t)n_nodes*sizeof(BranchTab);
+    off[4] = at; at += (size_t)n_nodes*MH_THREADS*sizeof(uint16_t);
+    at = (at + 15) & ~(size_t)15;
+    off[5] = at; at += (size_t)2*q_slots*MH_THREADS*sizeof(double);
+  }
+  else off[2] = off[3] = off[4] = off[5] = at;
+  return at;
+}
+
+template <int MAXN, int MAXJ, bool HALO, bool DEFER, bool QSMEM>
 __device__ __forceinline__ void
-mh_update_group(const PassArgs &a, const ModelParams &s_mp, const CtxTables &s_tb,
-                unsigned long long *s_dyn, uint64_t g) {
+mh_update_group(const PassArgs &a, const ModelParams &s_mp, const CtxTables &s_tb, const MhShared &sh, uint64_t g) {
   const int t = threadIdx.x, lane = t & 31;
   const int n_br = a.tree.n_nodes - 1;
   const uint64_t st = 3*g + a.colour;                          // the group's target site
   const int64_t gsite = a.global0 + (int64_t)st;
+  constexpr bool LOCK = mh_lock(MAXN);
 
   // interval stack / jump queue capacities grow with the tree (expected use ~ 0.1 / 0.07 per branch)
   constexpr int PB = MAXN <= 16 ? 16 : MAXN/2, QCAP = mh_qcap(MAXN);
-  FlatScratch<MAXN, PB, QCAP> S;
-  S.queue = reinterpret_cast<QSlot *>(s_dyn) + t*QCAP;
-  S.excl = reinterpret_cast<int *>(reinterpret_cast<QSlot *>(s_dyn) + MH_THREADS*QCAP) + (t & ~31);
   double pj_local[MAXJ];
-  uint16_t pn[MAXN];
+  uint16_t pn[MAXN];                   // generic routine / wide trees only
   uint8_t pend[MAXN];
   Proposal pr; pr.pj = pj_local; pr.cap = MAXJ; pr.pn = pn; pr.pend = pend;
   int accepted = 0, total = 0;
-  bool deferred = false;
-  {
-    const bool active = g < a.n_groups && st >= a.upd_lo && st < a.upd_hi && gsite >= 1 &&
-                        gsite + 1 < (int64_t)a.n_global;
-    SiteCtx c; c.pv = a.in; c.state = a.state; c.W = a.W; c.tree = a.tree; c.site = st;
-    int r = mh_site_flat<MAXN, PB, QCAP, HALO>(active, a.coop != 0, s_mp, s_tb, c, a.state, a.tri_llh, a.seed, a.sweep,
-                                         (uint64_t)gsite, a.n_global, S, pr, total);
+  bool deferred = false, local_pn = !LOCK;
+  typename LockMask<MAXN <= 64 ? MAXN : 64>::type propmask = 0, pend_bits = 0;
+  const bool active = g < a.n_groups && st >= a.upd_lo && st < a.upd_hi && gsite >= 1 &&
+                      gsite + 1 < (int64_t)a.n_global;
+  SiteCtx c; c.pv = a.in; c.state = a.state; c.W = a.W; c.tree = a.tree; c.site = st;
+  if constexpr (LOCK) {
+    LockScratch<MAXN, PB, QCAP, QSMEM> S;
+    S.queue = sh.queue + t*QCAP; S.excl = sh.excl + (t & ~31);
+    S.pn_s = sh.pn + t; S.q_s = sh.q + t;
+    int r = mh_site_lock<MAXN, PB, QCAP, HALO, QSMEM>(active, a.coop != 0, s_mp, s_tb, sh.tt, sh.bt, c, a.state, a.tri_llh,
+                                                      a.seed, a.sweep, (uint64_t)gsite, a.n_global, S, pj_local, MAXJ,
+                                                      pend_bits, propmask, total);
     if (DEFER) {
       if (r == -1 || r == -3) {
         a.ovf_list[1 + atomicAdd(a.ovf_list, 1u)] = (uint32_t)g;
@@ -94,11 +130,13 @@ mh_update_group(const PassArgs &a, const ModelParams &s_mp, const CtxTables &s_t
       // -3: interval stack too small -- a property of the neighbours' rows only, so switching
       // to the generic per-branch routine here is unbiased (rare; runs divergently)
       const bool generic = r == -3;
-      if (generic)
+      if (generic) {
         r = mh_site(s_mp, c, a.state, a.tri_llh, a.seed, a.sweep, (uint64_t)gsite, a.n_global,
-                    S.q, pr, total);
+                    S.q_local, pr, total);
+        local_pn = true;
+      }
       // -1: proposal longer than the per-thread buffer: rerun with a global scratch slot and
-      // the same streams (=> the same proposal).  The flat routine is warp-synchronous, so the
+      // the same streams (=> the same proposal).  The lockstep routine is warp-synchronous, so the
       // whole warp re-enters it with only the overflowing lanes active.
       if (__any_sync(0xffffffffu, r == -1)) {
         const bool again = r == -1;
@@ -108,14 +146,43 @@ mh_update_group(const PassArgs &a, const ModelParams &s_mp, const CtxTables &s_t
           else { pr.pj = a.scratch + (uint64_t)slot*a.scratch_cap; pr.cap = (int)a.scratch_cap; }
         }
         const bool redo = again && r == -1;
-        const int r2 = mh_site_flat<MAXN, PB, QCAP, HALO>(redo && !generic, a.coop != 0, s_mp, s_tb, c, a.state, a.tri_llh,
-                                                    a.seed, a.sweep, (uint64_t)gsite, a.n_global, S, pr, total);
-        if (redo && !generic) r = r2;
+        typename LockMask<MAXN>::type pm2 = 0, pe2 = 0; int tot2 = 0;
+        const int r2 = mh_site_lock<MAXN, PB, QCAP, HALO, QSMEM>(redo && !generic, a.coop != 0, s_mp, s_tb, sh.tt, sh.bt, c,
+                                                                 a.state, a.tri_llh, a.seed, a.sweep, (uint64_t)gsite,
+                                                                 a.n_global, S, pr.pj, pr.cap, pe2, pm2, tot2);
+        if (redo && !generic) { r = r2; propmask = pm2; pend_bits = pe2; total = tot2; }
         if (redo && generic)
           r = mh_site(s_mp, c, a.state, a.tri_llh, a.seed, a.sweep, (uint64_t)gsite, a.n_global,
-                      S.q, pr, total);
+                      S.q_local, pr, total);
         if (r == -1) { atomicOr(a.err, ERR_SCRATCH_SIZE); r = 0; }
       }
+    }
+    if (r == -2) { atomicOr(a.err, ERR_SAMPLER_STUCK); r = 0; }
+    if (r < 0) r = 0;
+    accepted = r;
+  }
+  else {
+    FlatScratch<MAXN, PB, QCAP> S;
+    S.queue = sh.queue + t*QCAP; S.excl = sh.excl + (t & ~31);
+    int r = mh_site_flat<MAXN, PB, QCAP, HALO>(active, a.coop != 0, s_mp, s_tb, c, a.state, a.tri_llh, a.seed, a.sweep,
+                                               (uint64_t)gsite, a.n_global, S, pr, total);
+    const bool generic = r == -3;
+    if (generic)
+      r = mh_site(s_mp, c, a.state, a.tri_llh, a.seed, a.sweep, (uint64_t)gsite, a.n_global, S.q, pr, total);
+    if (__any_sync(0xffffffffu, r == -1)) {
+      const bool again = r == -1;
+      if (again) {
+        const uint32_t slot = atomicAdd(a.scratch_ctr, 1u);
+        if (slot >= a.scratch_slots) { atomicOr(a.err, ERR_SCRATCH_SLOTS); r = 0; }
+        else { pr.pj = a.scratch + (uint64_t)slot*a.scratch_cap; pr.cap = (int)a.scratch_cap; }
+      }
+      const bool redo = again && r == -1;
+      const int r2 = mh_site_flat<MAXN, PB, QCAP, HALO>(redo && !generic, a.coop != 0, s_mp, s_tb, c, a.state, a.tri_llh,
+                                                        a.seed, a.sweep, (uint64_t)gsite, a.n_global, S, pr, total);
+      if (redo && !generic) r = r2;
+      if (redo && generic)
+        r = mh_site(s_mp, c, a.state, a.tri_llh, a.seed, a.sweep, (uint64_t)gsite, a.n_global, S.q, pr, total);
+      if (r == -1) { atomicOr(a.err, ERR_SCRATCH_SIZE); r = 0; }
     }
     if (r == -2) { atomicOr(a.err, ERR_SAMPLER_STUCK); r = 0; }
     if (r < 0) r = 0;
@@ -138,7 +205,11 @@ mh_update_group(const PassArgs &a, const ModelParams &s_mp, const CtxTables &s_t
         so = (uint32_t)at;
         double *blob = a.stage + at;
         uint16_t *cnt = reinterpret_cast<uint16_t *>(blob);
-        for (int bi = 0; bi < 4*hw; ++bi) cnt[bi] = bi < n_br ? pn[bi + 1] : 0;
+        for (int bi = 0; bi < 4*hw; ++bi) {
+          uint16_t n = 0;
+          if (bi < n_br) n = local_pn ? pn[bi + 1] : (((propmask >> (bi + 1)) & 1) ? sh.pn[(bi + 1)*MH_THREADS + t] : 0);
+          cnt[bi] = n;
+        }
         for (int k = 0; k < total; ++k) blob[hw + k] = pr.pj[k];
       }
     }
@@ -150,21 +221,33 @@ mh_update_group(const PassArgs &a, const ModelParams &s_mp, const CtxTables &s_t
 // routine on (a) the few groups next to a shard's ends, whose neighbours live in the halo store,
 // and (b) the overflow list of the main launch (a.list_mode; grid-stride over the list, whose
 // length is only known on the device).
-template <int MAXN, int MAXJ, bool HALO, bool DEFER = false>
+template <int MAXN, int MAXJ, bool HALO, bool DEFER, bool QSMEM>
 __global__ void __launch_bounds__(MH_THREADS, mh_minblocks(MAXN))
-mh_update_kernel(const PassArgs a) {
+mh_update_kernel(const PassArgs a, int q_slots) {
   __shared__ ModelParams s_mp;
   __shared__ CtxTables s_tb;
-  extern __shared__ unsigned long long s_dyn[];    // [MH_THREADS*QCAP] QSlot, then [MH_THREADS] int
+  extern __shared__ __align__(16) unsigned char s_dyn[];
   const int t = threadIdx.x;
   if (t == 0) s_mp = a.mp;
   fill_tables(a.mp, s_tb, t);
+  MhShared sh;
+  {
+    size_t off[6];
+    mh_smem_layout<MAXN>(a.tree.n_nodes, q_slots, off);
+    sh.queue = reinterpret_cast<QSlot *>(s_dyn + off[0]); sh.excl = reinterpret_cast<int *>(s_dyn + off[1]);
+    sh.tt = reinterpret_cast<TreeTab *>(s_dyn + off[2]); sh.bt = reinterpret_cast<BranchTab *>(s_dyn + off[3]);
+    sh.pn = reinterpret_cast<uint16_t *>(s_dyn + off[4]); sh.q = reinterpret_cast<double *>(s_dyn + off[5]);
+  }
   __syncthreads();
+  if (mh_lock(MAXN)) {
+    fill_lock_tables(s_mp, s_tb, a.tree, sh.tt, sh.bt, t, MH_THREADS);
+    __syncthreads();
+  }
   if (!HALO) {
     const uint64_t gi = (uint64_t)blockIdx.x*MH_THREADS + t;
     const uint64_t g = gi >= a.g_count ? a.n_groups                // group of sites 3g..3g+2
                                        : a.g_first + gi + (gi >= a.g_split ? a.g_skip : 0);
-    mh_update_group<MAXN, MAXJ, false, DEFER>(a, s_mp, s_tb, s_dyn, g);
+    mh_update_group<MAXN, MAXJ, false, DEFER, QSMEM>(a, s_mp, s_tb, sh, g);
   }
   else {
     const uint64_t n_items = a.list_mode ? (uint64_t)a.ovf_list[0] : a.g_count;
@@ -174,7 +257,7 @@ mh_update_kernel(const PassArgs a) {
       const uint64_t gi = base + t;
       uint64_t g = a.n_groups;
       if (gi < n_items) g = a.list_mode ? (uint64_t)a.ovf_list[1 + gi] : a.g_first + gi + (gi >= a.g_split ? a.g_skip : 0);
-      mh_update_group<MAXN, MAXJ, true, false>(a, s_mp, s_tb, s_dyn, g);
+      mh_update_group<MAXN, MAXJ, true, false, QSMEM>(a, s_mp, s_tb, sh, g);
       __syncwarp();
     }
   }
@@ -350,20 +433,49 @@ mh_pass_smem_bytes(int n_nodes) {
 
 // A sharded context reads its neighbours' boundary rows from the halo store; only the few
 // groups within two sites of the owned block's ends can touch it.  Those run in a small
-// launch of the halo-aware instantiation, everything else in the halo-free one (which is
-// 15 % faster: 5.5 vs 6.5 ms per pass).
-template <int MAXN, int MAXJ>
-static int
-launch_update_t(const PassArgs &a0, cudaStream_t st) {
-  const size_t smem = (size_t)MH_THREADS*mh_qcap(MAXN)*sizeof(QSlot) + MH_THREADS*sizeof(int);
-  PassArgs a = a0;
-  a.list_mode = 0;
+// launch of the halo-aware instantiation (launch_mh_edge), everything else in the halo-free one
+// (launch_mh_interior; 15 % faster: 5.5 vs 6.5 ms per pass).  The two launches touch disjoint groups
+// and may run concurrently on two streams (the multi-GPU driver starts the edge groups first so
+// that their rows can travel to the neighbour GPU while the interior is still being updated).
+static void
+edge_split(const PassArgs &a, uint64_t &g_lo, uint64_t &g_hi) {
   const uint64_t lo = a.in.own_lo, hi = a.in.own_hi;
-  uint64_t g_lo = lo == 0 ? 0 : (lo + 4)/3;                       // first group with 3g - 2 >= own_lo
-  uint64_t g_hi = hi == a.in.n_local ? a.n_groups : (hi >= 5 ? (hi - 5)/3 + 1 : 0);   // 3g + 4 < own_hi
+  g_lo = lo == 0 ? 0 : (lo + 4)/3;                                 // first group with 3g - 2 >= own_lo
+  g_hi = hi == a.in.n_local ? a.n_groups : (hi >= 5 ? (hi - 5)/3 + 1 : 0);   // 3g + 4 < own_hi
   g_lo = g_lo < a.n_groups ? g_lo : a.n_groups;
   g_hi = g_hi > g_lo ? g_hi : g_lo;
   g_hi = g_hi < a.n_groups ? g_hi : a.n_groups;
+}
+
+// Shared memory per CTA that still lets mh_minblocks(MAXN) CTAs share an SM (227 KB usable, 1 KB
+// reserved per CTA, ~0.4 KB static).
+template <int MAXN>
+static size_t smem_budget() { return (size_t)(232448 - 1024*mh_minblocks(MAXN))/mh_minblocks(MAXN) - 512; }
+
+template <int MAXN, int MAXJ, bool HALO, bool DEFER>
+static void
+launch_variant(const PassArgs &a, unsigned blocks, cudaStream_t st) {
+  size_t off[6];
+  const bool qsmem = mh_lock(MAXN) && mh_smem_layout<MAXN>(a.tree.n_nodes, a.q_slots, off) <= smem_budget<MAXN>();
+  if (qsmem) {
+    const size_t smem = mh_smem_layout<MAXN>(a.tree.n_nodes, a.q_slots, off);
+    cudaFuncSetAttribute(mh_update_kernel<MAXN, MAXJ, HALO, DEFER, mh_lock(MAXN)>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    mh_update_kernel<MAXN, MAXJ, HALO, DEFER, mh_lock(MAXN)><<<blocks, MH_THREADS, smem, st>>>(a, a.q_slots);
+  }
+  else {
+    const size_t smem = mh_smem_layout<MAXN>(a.tree.n_nodes, 0, off);
+    cudaFuncSetAttribute(mh_update_kernel<MAXN, MAXJ, HALO, DEFER, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    mh_update_kernel<MAXN, MAXJ, HALO, DEFER, false><<<blocks, MH_THREADS, smem, st>>>(a, 0);
+  }
+}
+
+template <int MAXN, int MAXJ>
+static int
+launch_interior_t(const PassArgs &a0, cudaStream_t st) {
+  PassArgs a = a0;
+  a.list_mode = 0;
+  uint64_t g_lo, g_hi; edge_split(a, g_lo, g_hi);
+  if (g_hi <= g_lo) return 0;
   // deferral costs one more launch whose length is the latency of a single site update (~0.1 ms
   // when a handful of sites overflow): worth it only when the pass is long (1e6-site single branch:
   // 0.45 vs 0.41 ms per pass with it)
@@ -371,45 +483,52 @@ launch_update_t(const PassArgs &a0, cudaStream_t st) {
   const char *env = getenv("EPIEVO_B200_DEFER_MIN");
   const uint64_t defer_min = env ? strtoull(env, nullptr, 10) : (1ull << 20);
   const bool defer = mh_defer(MAXN) && g_hi - g_lo >= defer_min;
-  if (g_hi > g_lo) {
-    a.g_first = g_lo; a.g_count = a.g_split = g_hi - g_lo; a.g_skip = 0;
-    const unsigned blocks = (unsigned)((a.g_count + MH_THREADS - 1)/MH_THREADS);
-    if (defer) {
-      cudaFuncSetAttribute(mh_update_kernel<MAXN, MAXJ, false, mh_defer(MAXN)>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      mh_update_kernel<MAXN, MAXJ, false, mh_defer(MAXN)><<<blocks, MH_THREADS, smem, st>>>(a);
-    }
-    else {
-      cudaFuncSetAttribute(mh_update_kernel<MAXN, MAXJ, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      mh_update_kernel<MAXN, MAXJ, false, false><<<blocks, MH_THREADS, smem, st>>>(a);
-    }
-  }
-  int launches = (g_hi > g_lo);
-  if (g_hi > g_lo && defer) {
-    // the sites the main launch deferred (list length known on the device only)
-    a.list_mode = 1;
-    cudaFuncSetAttribute(mh_update_kernel<MAXN, MAXJ, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    mh_update_kernel<MAXN, MAXJ, true><<<MH_OVF_BLOCKS, MH_THREADS, smem, st>>>(a);
-    a.list_mode = 0;
-    ++launches;
-  }
+  a.g_first = g_lo; a.g_count = a.g_split = g_hi - g_lo; a.g_skip = 0;
+  const unsigned blocks = (unsigned)((a.g_count + MH_THREADS - 1)/MH_THREADS);
+  if (defer) launch_variant<MAXN, MAXJ, false, mh_defer(MAXN)>(a, blocks, st);
+  else launch_variant<MAXN, MAXJ, false, false>(a, blocks, st);
+  if (!defer) return 1;
+  // the sites the main launch deferred (list length known on the device only)
+  a.list_mode = 1;
+  launch_variant<MAXN, MAXJ, true, false>(a, MH_OVF_BLOCKS, st);
+  return 2;
+}
+
+template <int MAXN, int MAXJ>
+static int
+launch_edge_t(const PassArgs &a0, cudaStream_t st) {
+  PassArgs a = a0;
+  a.list_mode = 0;
+  uint64_t g_lo, g_hi; edge_split(a, g_lo, g_hi);
   const uint64_t n_edge = g_lo + (a.n_groups - g_hi);
-  if (n_edge) {
-    a.g_first = 0; a.g_split = g_lo; a.g_skip = g_hi - g_lo; a.g_count = n_edge;
-    const unsigned blocks = (unsigned)((n_edge + MH_THREADS - 1)/MH_THREADS);
-    cudaFuncSetAttribute(mh_update_kernel<MAXN, MAXJ, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    mh_update_kernel<MAXN, MAXJ, true><<<blocks, MH_THREADS, smem, st>>>(a);
-    ++launches;
-  }
-  return launches;
+  if (!n_edge) return 0;
+  a.g_first = 0; a.g_split = g_lo; a.g_skip = g_hi - g_lo; a.g_count = n_edge;
+  launch_variant<MAXN, MAXJ, true, false>(a, (unsigned)((n_edge + MH_THREADS - 1)/MH_THREADS), st);
+  return 1;
+}
+
+int
+launch_mh_interior(const PassArgs &a, cudaStream_t st) {
+  const int n = a.tree.n_nodes;
+  if (n <= 8) return launch_interior_t<8, 16>(a, st);
+  if (n <= 16) return launch_interior_t<16, 32>(a, st);
+  if (n <= 64) return launch_interior_t<64, 64>(a, st);
+  return launch_interior_t<256, 128>(a, st);
+}
+
+int
+launch_mh_edge(const PassArgs &a, cudaStream_t st) {
+  const int n = a.tree.n_nodes;
+  if (n <= 8) return launch_edge_t<8, 16>(a, st);
+  if (n <= 16) return launch_edge_t<16, 32>(a, st);
+  if (n <= 64) return launch_edge_t<64, 64>(a, st);
+  return launch_edge_t<256, 128>(a, st);
 }
 
 int
 launch_mh_pass(const PassArgs &a, cudaStream_t st) {
-  const int n = a.tree.n_nodes;
-  if (n <= 8) return launch_update_t<8, 16>(a, st);
-  if (n <= 16) return launch_update_t<16, 32>(a, st);
-  if (n <= 64) return launch_update_t<64, 64>(a, st);
-  return launch_update_t<256, 128>(a, st);
+  const int n = launch_mh_interior(a, st);
+  return n + launch_mh_edge(a, st);
 }
 
 void

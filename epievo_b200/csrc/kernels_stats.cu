@@ -574,10 +574,10 @@ export_kernel(const PathView pv, const uint8_t *state, int W, uint64_t n_sites, 
 }
 
 __global__ void
-scale_halo_kernel(double *hjmp, int n_br, const double *scale) {
+scale_halo_kernel(double *hjmp, int n_br, int halo_k, const double *scale) {
   const int row = blockIdx.x;                     // slot*n_br + bi
   const double sc = scale[row % n_br + 1];
-  for (int k = threadIdx.x; k < HALO_K; k += blockDim.x) hjmp[(size_t)row*HALO_K + k] *= sc;
+  for (int k = threadIdx.x; k < halo_k; k += blockDim.x) hjmp[(size_t)row*halo_k + k] *= sc;
 }
 
 }  // namespace
@@ -662,11 +662,11 @@ launch_axpy_stats(double *Js, double *Ds, const double *J, const double *D, int 
 
 void
 launch_scale_jumps(double *jmp, const uint64_t *jbase, const uint32_t *off, uint64_t pitch,
-                   uint64_t n_own, int n_branches, const double *scale, double *hjmp,
+                   uint64_t n_own, int n_branches, const double *scale, double *hjmp, int halo_k,
                    cudaStream_t st) {
   dim3 grid(592, n_branches);
   scale_kernel<<<grid, 256, 0, st>>>(jmp, jbase, off, pitch, n_own, scale);
-  scale_halo_kernel<<<2*HALO_W*n_branches, 64, 0, st>>>(hjmp, n_branches, scale);
+  scale_halo_kernel<<<2*HALO_W*n_branches, 64, 0, st>>>(hjmp, n_branches, halo_k, scale);
 }
 
 void

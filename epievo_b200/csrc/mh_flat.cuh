@@ -72,14 +72,14 @@ row_data(const PathView &pv, int bi, uint64_t site, const double *&ptr, int &n) 
   else {
     const int slot = site < pv.own_lo ? (int)site : HALO_W + (int)(site - pv.own_hi);
     n = pv.hcnt[slot*pv.n_br + bi];
-    ptr = pv.hjmp + (size_t)(slot*pv.n_br + bi)*HALO_K;
+    ptr = pv.hjmp + (size_t)(slot*pv.n_br + bi)*pv.halo_k;
   }
 }
 
 // Rows of sites s-1, s, s+1 on branch bi (own row: count only).
-template <bool HALO, int WORDS>
+template <bool HALO, typename SW>
 __device__ __forceinline__ void
-load_lmr(const PathView &pv, const StateWin<WORDS> &sw, int bi, uint64_t site,
+load_lmr(const PathView &pv, const SW &sw, int bi, uint64_t site,
          Row &L, Row &R, int &own_n) {
   L.init = sw.bit(-1, bi + 1);
   R.init = sw.bit(1, bi + 1);

@@ -26,7 +26,7 @@ load_row(const PathView &pv, const uint8_t *state, int W, int bi, uint64_t site)
   else {
     const int slot = site < pv.own_lo ? (int)site : HALO_W + (int)(site - pv.own_hi);
     r.n = pv.hcnt[slot*pv.n_br + bi];
-    r.ptr = pv.hjmp + (size_t)(slot*pv.n_br + bi)*HALO_K;
+    r.ptr = pv.hjmp + (size_t)(slot*pv.n_br + bi)*pv.halo_k;
   }
   return r;
 }

@@ -205,6 +205,24 @@ class Context:
     def halo_unpack(self, colour: int, rec_lo_ptr: Optional[int], rec_hi_ptr: Optional[int]):
         self._ck(self.lib.epv_halo_unpack(self.h, colour, C.c_void_p(rec_lo_ptr), C.c_void_p(rec_hi_ptr)))
 
+    def halo_capacity(self) -> Tuple[int, int]:
+        """(jump capacity of a halo row, capacity the packed boundary rows ask for)."""
+        cap, need = C.c_uint64(), C.c_uint64()
+        self._ck(self.lib.epv_halo_capacity(self.h, C.byref(cap), C.byref(need)))
+        return cap.value, need.value
+
+    def halo_set_capacity(self, capacity: int):
+        self._ck(self.lib.epv_halo_set_capacity(self.h, capacity))
+
+    def set_side_stream(self, cuda_stream_ptr: int):
+        self._ck(self.lib.epv_set_side_stream(self.h, C.c_void_p(cuda_stream_ptr)))
+
+    def pass_begin(self, colour: int, seed: int, sweep_idx: int, rec_lo_ptr: Optional[int], rec_hi_ptr: Optional[int]):
+        self._ck(self.lib.epv_pass_begin(self.h, colour, seed, sweep_idx, C.c_void_p(rec_lo_ptr), C.c_void_p(rec_hi_ptr)))
+
+    def pass_end(self, colour: int, rec_lo_ptr: Optional[int], rec_hi_ptr: Optional[int]):
+        self._ck(self.lib.epv_pass_end(self.h, colour, C.c_void_p(rec_lo_ptr), C.c_void_p(rec_hi_ptr)))
+
     # -- statistics -----------------------------------------------------------------
     def suffstats(self):
         J = np.zeros(self.n_nodes * 8)
@@ -296,3 +314,102 @@ class Context:
         ms = C.c_double()
         self._ck(self.lib.epv_rebuild_kernel_time(self.h, C.byref(ms)))
         return ms.value
+
+
+class MultiContext:
+    """Several GPUs behind one handle in one process (epv_multi_*, csrc/api_multi.cu): the calls of
+    Context with the same meaning, over contiguous site blocks with peer-copied halo records."""
+
+    def __init__(self, n_shards: int, devices=None):
+        self.lib = L.load()
+        self.h = L.ctx_p()
+        dev = None
+        if devices is not None:
+            assert len(devices) == n_shards
+            dev = (C.c_int * n_shards)(*devices)
+        if self.lib.epv_multi_create(C.byref(self.h), n_shards, dev) != 0:
+            self.h = None
+            raise EpvError("epv_multi_create failed (no usable CUDA devices; there is no CPU fallback)")
+        self.n_shards = n_shards
+        self.n_nodes = 0
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.epv_multi_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc: int):
+        if rc != 0:
+            raise EpvError(self.lib.epv_multi_last_error(self.h).decode())
+
+    def set_tree(self, tree: Tree):
+        ss = np.ascontiguousarray(tree.subtree_sizes, np.uint64)
+        pi = np.ascontiguousarray(tree.parent_ids, np.uint64)
+        self._ck(self.lib.epv_multi_set_tree(self.h, tree.n_nodes, _u64(ss), _u64(pi), _d(_f64(tree.branches))))
+        self.n_nodes = tree.n_nodes
+
+    def set_model(self, rates, T):
+        self._ck(self.lib.epv_multi_set_model(self.h, _d(_f64(rates)), _d(_f64(T))))
+
+    def upload_paths(self, ps: PathSet):
+        j = ps.jumps if len(ps.jumps) else np.zeros(1)
+        self._ck(self.lib.epv_multi_upload_paths(self.h, ps.n_sites, ps.n_nodes, _u8(ps.init_state),
+                                                 _u64(ps.row_off), _d(j), _d(ps.tot_time)))
+
+    def upload_raw(self, n_sites, n_nodes, init_ptr, off_ptr, jumps_ptr, tot_time):
+        self._ck(self.lib.epv_multi_upload_paths(
+            self.h, n_sites, n_nodes, C.cast(init_ptr, L.u8p), C.cast(off_ptr, L.u64p),
+            C.cast(jumps_ptr, L.dp), _d(_f64(tot_time))))
+
+    def paths_size(self) -> Tuple[int, int, int]:
+        a, b, c = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        self._ck(self.lib.epv_multi_paths_size(self.h, C.byref(a), C.byref(b), C.byref(c)))
+        return a.value, b.value, c.value
+
+    def download_paths(self, node_names=()) -> PathSet:
+        n_sites, n_nodes, n_jumps = self.paths_size()
+        init = np.zeros(n_sites * n_nodes, np.uint8)
+        off = np.zeros(n_sites * n_nodes + 1, np.uint64)
+        jumps = np.zeros(max(1, n_jumps))
+        tot = np.zeros(n_nodes)
+        self._ck(self.lib.epv_multi_download_paths(self.h, _u8(init), _u64(off), _d(jumps), _d(tot)))
+        return PathSet(n_sites, n_nodes, init, off, jumps[:n_jumps].copy(), tot, list(node_names))
+
+    def reset(self):
+        self._ck(self.lib.epv_multi_reset(self.h))
+
+    def sweep(self, seed: int, sweep_idx: int) -> int:
+        n = C.c_uint64()
+        self._ck(self.lib.epv_multi_sweep(self.h, seed, sweep_idx, C.byref(n)))
+        return n.value
+
+    def run_mcmc(self, burn_in: int, batch: int, seed: int, first_sweep: int = 0):
+        J, D, acc = np.zeros(self.n_nodes * 8), np.zeros(self.n_nodes * 8), C.c_double()
+        self._ck(self.lib.epv_multi_run_mcmc(self.h, burn_in, batch, seed, first_sweep, _d(J), _d(D), C.byref(acc)))
+        return J.reshape(-1, 8), D.reshape(-1, 8), acc.value
+
+    def suffstats(self):
+        J, D = np.zeros(self.n_nodes * 8), np.zeros(self.n_nodes * 8)
+        self._ck(self.lib.epv_multi_suffstats(self.h, _d(J), _d(D)))
+        return J.reshape(-1, 8), D.reshape(-1, 8)
+
+    def scale_jump_times(self, new_branches):
+        self._ck(self.lib.epv_multi_scale_jump_times(self.h, _d(_f64(new_branches))))
+
+    def mcem_iteration(self, burn_in, batch, seed, first_sweep, rates, T, branches,
+                       optimize_branches=False, param_tol=1e-10):
+        r, t, br, bl = _f64(rates).copy(), _f64(T).copy(), _f64(branches).copy(), np.zeros(4)
+        acc, llh = C.c_double(), C.c_double()
+        self._ck(self.lib.epv_multi_mcem_iteration(self.h, burn_in, batch, seed, first_sweep,
+                                                   int(optimize_branches), param_tol, _d(r), _d(t), _d(br),
+                                                   _d(bl), C.byref(acc), C.byref(llh)))
+        return r, t, br, bl, acc.value, llh.value
+
+    def launch_count(self) -> int:
+        return int(self.lib.epv_multi_launch_count(self.h))

@@ -17,9 +17,17 @@
  *  - scan order: sites are updated in three stride-3 colour classes per sweep instead
  *    of 1..n-2 sequentially;
  *  - Metropolis_Hastings_site(site_id): the GPU updates whole sweeps.  The call with
- *    site_id == 1 runs one full sweep over sites 1..n-2, calls with other site ids are
- *    no-ops, so the caller's `for site_id in 1..n-2` loop
- *    (prog/epievo_sim_pairwise.cpp:268-270) performs exactly one sweep, as before.
+ *    site_id == 1 runs one full sweep over sites 1..n-2, calls with other site ids do no
+ *    work, so the caller's `for site_id in 1..n-2` loop
+ *    (prog/epievo_sim_pairwise.cpp:268-270) performs exactly one sweep, as before.  The
+ *    return values of one such loop add up to the sweep's number of accepted updates
+ *    (true for site ids 1..n_accepted), not site by site;
+ *  - SAMPLE_ROOT must stay false (its value in every caller, SingleSiteSampler.cpp:441):
+ *    the device sampler's acceptance ratio relies on the root state being kept; run_mcmc /
+ *    Metropolis_Hastings_site throw std::runtime_error otherwise;
+ *  - EPIEVO_B200_GPUS=N shards the sites over N GPUs of the box (contiguous blocks, halo
+ *    records over NVLink, include/epievo_b200.h epv_multi_*); EPIEVO_B200_DEVICE=k picks
+ *    the (first) device.  The chain does not depend on N.
  */
 #ifndef SINGLE_SITE_SAMPLER_HPP
 #define SINGLE_SITE_SAMPLER_HPP
@@ -32,7 +40,7 @@
 #include "EpiEvoModel.hpp"
 #include "TreeHelper.hpp"
 
-struct epv_ctx;
+struct epv_multi;
 
 class SingleSiteSampler {
 public:
@@ -69,8 +77,9 @@ private:
   void download(std::vector<std::vector<Path> > &paths);
   void check(int rc) const;
 
-  epv_ctx *ctx;
+  epv_multi *ctx;          // one handle over EPIEVO_B200_GPUS contexts (default 1)
   size_t sweep_counter;
+  size_t last_sweep_accepts;
   // flat exchange buffers, reused across calls
   std::vector<unsigned char> init_state;
   std::vector<unsigned long long> row_off;

@@ -4,46 +4,73 @@
  * node-major CSR exchange format, call the device path, unflatten. */
 #include "SingleSiteSampler.hpp"
 
+#include <algorithm>
 #include <cstdlib>
 #include <stdexcept>
 #include <string>
+#include <thread>
 
 #include "epievo_b200.h"
 
 using std::vector;
 
 static int
-device_from_env() {
-  const char *e = std::getenv("EPIEVO_B200_DEVICE");
-  return e ? std::atoi(e) : 0;
+int_from_env(const char *name, int dflt) {
+  const char *e = std::getenv(name);
+  return e && *e ? std::atoi(e) : dflt;
 }
 
-static epv_ctx *
+static epv_multi *
 new_context() {
-  epv_ctx *c = nullptr;
-  if (epv_create(&c, device_from_env()) != 0 || !c)
-    throw std::runtime_error("epievo_b200: no usable CUDA device (there is no CPU fallback)");
+  const int first = int_from_env("EPIEVO_B200_DEVICE", 0), n = std::max(1, int_from_env("EPIEVO_B200_GPUS", 1));
+  std::vector<int> dev(n);
+  for (int r = 0; r < n; ++r) dev[r] = first + r;
+  epv_multi *c = nullptr;
+  if (epv_multi_create(&c, n, dev.data()) != 0 || !c)
+    throw std::runtime_error("epievo_b200: no usable CUDA device(s) (EPIEVO_B200_DEVICE / EPIEVO_B200_GPUS; "
+                             "there is no CPU fallback)");
   return c;
 }
 
 SingleSiteSampler::SingleSiteSampler(const size_t n_burn_in, const size_t n_batch) :
   SAMPLE_ROOT(false), burn_in(n_burn_in), batch(n_batch), ctx(new_context()),
-  sweep_counter(0) {}
+  sweep_counter(0), last_sweep_accepts(0) {}
 
-SingleSiteSampler::~SingleSiteSampler() { epv_destroy(ctx); }
+SingleSiteSampler::~SingleSiteSampler() { epv_multi_destroy(ctx); }
 
 void
 SingleSiteSampler::check(int rc) const {
-  if (rc != 0) throw std::runtime_error(std::string("epievo_b200: ") + epv_last_error(ctx));
+  if (rc != 0) throw std::runtime_error(std::string("epievo_b200: ") + epv_multi_last_error(ctx));
 }
 
 void
 SingleSiteSampler::configure(const EpiEvoModel &the_model, const TreeHelper &th) {
+  if (SAMPLE_ROOT)
+    throw std::runtime_error("epievo_b200: SAMPLE_ROOT = true is not supported (the device sampler keeps "
+                             "the root state, as every caller of the reference does)");
   vector<uint64_t> ss(th.subtree_sizes.begin(), th.subtree_sizes.end());
   vector<uint64_t> pi(th.parent_ids.begin(), th.parent_ids.end());
-  check(epv_set_tree(ctx, th.n_nodes, ss.data(), pi.data(), th.branches.data()));
+  check(epv_multi_set_tree(ctx, th.n_nodes, ss.data(), pi.data(), th.branches.data()));
   const double T[4] = {the_model.T(0, 0), the_model.T(0, 1), the_model.T(1, 0), the_model.T(1, 1)};
-  check(epv_set_model(ctx, the_model.triplet_rates.data(), T));
+  check(epv_multi_set_model(ctx, the_model.triplet_rates.data(), T));
+}
+
+/* Site ranges handled by the host threads of flatten / unflatten (one heap vector per row makes
+ * both memory-latency bound; at 1e6 sites they were the largest term of a run_mcmc call). */
+static size_t
+host_threads(size_t n_rows) {
+  const size_t hw = std::max(1u, std::thread::hardware_concurrency());
+  return n_rows < 200000 ? 1 : std::min<size_t>(hw, 32);
+}
+
+template <typename F>
+static void
+for_site_ranges(size_t n_sites, size_t n_threads, F f) {
+  if (n_threads <= 1) { f(0, 0, n_sites); return; }
+  std::vector<std::thread> th;
+  for (size_t t = 0; t < n_threads; ++t)
+    th.emplace_back(f, t, n_sites*t/n_threads, n_sites*(t + 1)/n_threads);
+  for (size_t t = 0; t < th.size(); ++t) th[t].join();
 }
 
 /* [site][node] -> node-major CSR (the order of the local-paths file, Path.cpp:123-148) */
@@ -53,43 +80,52 @@ SingleSiteSampler::upload(const vector<vector<Path> > &paths, const TreeHelper &
   init_state.assign(n_sites*n_nodes, 0);
   row_off.assign(n_sites*n_nodes + 1, 0);
   tot_time.assign(n_nodes, 0.0);
+  for (size_t b = 1; b < n_nodes; ++b) tot_time[b] = paths[0][b].tot_time;
+  const size_t T = host_threads(n_sites*n_nodes);
+  // jumps per (node, thread) -> where every thread's rows of every node start
+  vector<size_t> cnt(n_nodes*T, 0);
+  for_site_ranges(n_sites, T, [&](size_t t, size_t s0, size_t s1) {
+    for (size_t s = s0; s < s1; ++s)
+      for (size_t b = 1; b < n_nodes; ++b) cnt[b*T + t] += paths[s][b].jumps.size();
+  });
   size_t total = 0;
-  for (size_t b = 1; b < n_nodes; ++b)
-    for (size_t s = 0; s < n_sites; ++s) total += paths[s][b].jumps.size();
+  for (size_t i = T; i < n_nodes*T; ++i) { const size_t c = cnt[i]; cnt[i] = total; total += c; }
   jumps.resize(total ? total : 1);
-  size_t k = 0;
-  for (size_t s = 0; s < n_sites; ++s) row_off[s] = 0;
-  for (size_t b = 1; b < n_nodes; ++b) {
-    tot_time[b] = paths[0][b].tot_time;
-    for (size_t s = 0; s < n_sites; ++s) {
-      const Path &p = paths[s][b];
-      const size_t r = b*n_sites + s;
-      init_state[r] = p.init_state;
-      row_off[r] = k;
-      for (size_t j = 0; j < p.jumps.size(); ++j) jumps[k++] = p.jumps[j];
+  for_site_ranges(n_sites, T, [&](size_t t, size_t s0, size_t s1) {
+    for (size_t b = 1; b < n_nodes; ++b) {
+      size_t k = cnt[b*T + t];
+      for (size_t s = s0; s < s1; ++s) {
+        const Path &p = paths[s][b];
+        const size_t r = b*n_sites + s;
+        init_state[r] = p.init_state;
+        row_off[r] = k;
+        for (size_t j = 0; j < p.jumps.size(); ++j) jumps[k++] = p.jumps[j];
+      }
     }
-  }
-  row_off[n_sites*n_nodes] = k;
-  check(epv_upload_paths(ctx, n_sites, n_nodes, init_state.data(),
-                         reinterpret_cast<const uint64_t *>(row_off.data()), jumps.data(),
-                         tot_time.data()));
+  });
+  row_off[n_sites*n_nodes] = total;
+  check(epv_multi_upload_paths(ctx, n_sites, n_nodes, init_state.data(),
+                               reinterpret_cast<const uint64_t *>(row_off.data()), jumps.data(),
+                               tot_time.data()));
 }
 
 void
 SingleSiteSampler::download(vector<vector<Path> > &paths) {
   uint64_t n_sites = 0, n_nodes = 0, n_jumps = 0;
-  check(epv_paths_size(ctx, &n_sites, &n_nodes, &n_jumps));
+  check(epv_multi_paths_size(ctx, &n_sites, &n_nodes, &n_jumps));
   jumps.resize(n_jumps ? n_jumps : 1);
-  check(epv_download_paths(ctx, init_state.data(), reinterpret_cast<uint64_t *>(row_off.data()),
-                           jumps.data(), tot_time.data()));
-  for (size_t b = 1; b < n_nodes; ++b)
-    for (size_t s = 0; s < n_sites; ++s) {
-      const size_t r = b*n_sites + s;
-      Path &p = paths[s][b];
-      p.init_state = init_state[r] != 0;
-      p.tot_time = tot_time[b];
-      p.jumps.assign(jumps.begin() + row_off[r], jumps.begin() + row_off[r + 1]);
-    }
+  check(epv_multi_download_paths(ctx, init_state.data(), reinterpret_cast<uint64_t *>(row_off.data()),
+                                 jumps.data(), tot_time.data()));
+  for_site_ranges(n_sites, host_threads(n_sites*n_nodes), [&](size_t, size_t s0, size_t s1) {
+    for (size_t s = s0; s < s1; ++s)
+      for (size_t b = 1; b < n_nodes; ++b) {
+        const size_t r = b*n_sites + s;
+        Path &p = paths[s][b];
+        p.init_state = init_state[r] != 0;
+        p.tot_time = tot_time[b];
+        p.jumps.assign(jumps.begin() + row_off[r], jumps.begin() + row_off[r + 1]);
+      }
+  });
 }
 
 /* The reference caches tri_llh here (SingleSiteSampler.cpp:449-475).  The device cache
@@ -107,12 +143,14 @@ bool
 SingleSiteSampler::Metropolis_Hastings_site(const EpiEvoModel &the_model, const TreeHelper &th,
                                             const size_t site_id,
                                             vector<vector<Path> > &paths, std::mt19937 &gen) {
-  if (site_id != 1) return true;      // see the header: one sweep per caller loop
+  // see the header: one sweep per caller loop; the loop's return values add up to the accept count
+  if (site_id != 1) return site_id <= last_sweep_accepts;
   configure(the_model, th);
   upload(paths, th);
   uint64_t n_acc = 0;
-  check(epv_sweep(ctx, seed_from(gen), sweep_counter++, &n_acc));
+  check(epv_multi_sweep(ctx, seed_from(gen), sweep_counter++, &n_acc));
   download(paths);
+  last_sweep_accepts = n_acc;
   return n_acc > 0;
 }
 
@@ -124,8 +162,8 @@ SingleSiteSampler::run_mcmc(const EpiEvoModel &the_model, const TreeHelper &th,
   configure(the_model, th);
   upload(paths, th);
   vector<double> J(th.n_nodes*8), D(th.n_nodes*8);
-  check(epv_run_mcmc(ctx, burn_in, batch, seed_from(gen), sweep_counter, J.data(), D.data(),
-                     &acceptance_rate));
+  check(epv_multi_run_mcmc(ctx, burn_in, batch, seed_from(gen), sweep_counter, J.data(), D.data(),
+                           &acceptance_rate));
   sweep_counter += burn_in + batch;
   download(paths);
   J_all_sites.assign(th.n_nodes, vector<double>(8, 0.0));   // row 0 unused, as the reference
@@ -145,7 +183,7 @@ get_sufficient_statistics(const vector<vector<Path> > &all_paths, const TreeHelp
                           vector<vector<double> > &J, vector<vector<double> > &D) {
   // a throw-away context: tree + paths only (no model needed for J/D)
   epv_ctx *c = nullptr;
-  if (epv_create(&c, device_from_env()) != 0 || !c)
+  if (epv_create(&c, int_from_env("EPIEVO_B200_DEVICE", 0)) != 0 || !c)
     throw std::runtime_error("epievo_b200: no usable CUDA device (there is no CPU fallback)");
   struct Guard { epv_ctx *c; ~Guard() { epv_destroy(c); } } guard{c};
   auto ck = [&](int rc) { if (rc) throw std::runtime_error(std::string("epievo_b200: ") + epv_last_error(c)); };

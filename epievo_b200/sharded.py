@@ -42,16 +42,36 @@ def local_paths(ps: PathSet, n_global: int, world: int, rank: int) -> PathSet:
 
 
 class Shard:
-    """One context + its four device-side halo records."""
+    """One context + its four device-side halo records + the side stream its halo traffic runs on."""
 
-    def __init__(self, ctx, n_global: int, world: int, rank: int, torch_device):
+    def __init__(self, ctx, n_global: int, world: int, rank: int, torch_device, side_stream=None):
         import torch
         self.ctx, self.rank, self.world, self.n_global = ctx, rank, world, n_global
+        self.device = torch_device
         self.lo, self.hi, self.halo_lo, self.halo_hi = shard_bounds(n_global, world, rank)
         ctx.set_shard(n_global, self.lo, self.hi, self.halo_lo, self.halo_hi)
-        nb = ctx.halo_record_bytes()
-        mk = lambda: torch.zeros(nb, dtype=torch.uint8, device=torch_device)
+        # a torch stream, so that NCCL send/recv (or the test's tensor copies) can be enqueued on it
+        self.side = side_stream if side_stream is not None else torch.cuda.Stream(device=torch_device)
+        ctx.set_side_stream(self.side.cuda_stream)
+        self.rec_bytes = 0
+        self.ensure_records()
+
+    def ensure_records(self):
+        """(Re)allocates the records for the context's current halo-row capacity."""
+        import torch
+        nb = self.ctx.halo_record_bytes()
+        if nb == self.rec_bytes:
+            return
+        self.ctx.synchronize()
+        mk = lambda: torch.zeros(nb, dtype=torch.uint8, device=self.device)
         self.send_lo, self.send_hi, self.recv_lo, self.recv_hi = mk(), mk(), mk(), mk()
+        self.rec_bytes = nb
+
+    def begin(self, colour, seed, sweep):
+        self.ctx.pass_begin(colour, seed, sweep, self._p(self.send_lo, self.halo_lo), self._p(self.send_hi, self.halo_hi))
+
+    def end(self, colour):
+        self.ctx.pass_end(colour, self._p(self.recv_lo, self.halo_lo), self._p(self.recv_hi, self.halo_hi))
 
     def _p(self, t, present):
         return t.data_ptr() if present else None
@@ -70,6 +90,10 @@ class DistExchange:
         self.s = shard
 
     def exchange(self):
+        """ncclSend/ncclRecv pairs with the two ring neighbours, enqueued on the shard's SIDE stream
+        (behind the pack of epv_pass_begin, ahead of the unpack of epv_pass_end): nothing here blocks
+        the host or the main stream."""
+        import torch
         import torch.distributed as dist
         s, ops = self.s, []
         if s.halo_lo:
@@ -77,8 +101,20 @@ class DistExchange:
         if s.halo_hi:
             ops += [dist.P2POp(dist.isend, s.send_hi, s.rank + 1), dist.P2POp(dist.irecv, s.recv_hi, s.rank + 1)]
         if ops:
-            for w in dist.batch_isend_irecv(ops):
-                w.wait()
+            if s.side is None:                      # CPU stand-in shards (gloo tests)
+                for w in dist.batch_isend_irecv(ops):
+                    w.wait()
+                return
+            with torch.cuda.stream(s.side):
+                for w in dist.batch_isend_irecv(ops):
+                    w.wait()
+
+    def allreduce_max(self, value: int) -> int:
+        import torch
+        import torch.distributed as dist
+        t = torch.tensor([value], dtype=torch.int64, device=self.s.device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return int(t.item())
 
     def allreduce_sum(self, arr: np.ndarray) -> np.ndarray:
         import torch
@@ -95,12 +131,36 @@ class LocalExchange:
         self.shards = list(shards)
 
     def exchange(self):
-        for a, b in zip(self.shards[:-1], self.shards[1:]):
-            b.recv_lo.copy_(a.send_hi)
-            a.recv_hi.copy_(b.send_lo)
+        """Record copies on the first shard's side stream, ordered after every shard's pack and before
+        every shard's unpack."""
+        import torch
+        main = self.shards[0].side
+        for s in self.shards[1:]:
+            if s.side is not main:
+                main.wait_stream(s.side)
+        with torch.cuda.stream(main):
+            for a, b in zip(self.shards[:-1], self.shards[1:]):
+                b.recv_lo.copy_(a.send_hi)
+                a.recv_hi.copy_(b.send_lo)
+        for s in self.shards[1:]:
+            if s.side is not main:
+                s.side.wait_stream(main)
+
+    def allreduce_max(self, value: int) -> int:
+        return value
 
 
-def colour_pass(shards: Sequence[Shard], transport, colour: int, seed: int, sweep: int):
+def colour_pass(shards: Sequence[Shard], transport, colour: int, seed: int, sweep: int, overlap: bool = True):
+    """One colour pass over the shards.  overlap: epv_pass_begin / exchange on the side streams /
+    epv_pass_end (edge groups first, the records travel while the interior is updated); otherwise the
+    serial protocol epv_pass -> pack -> exchange -> unpack on one stream.  Same chain either way."""
+    if overlap:
+        for s in shards:
+            s.begin(colour, seed, sweep)
+        transport.exchange()
+        for s in shards:
+            s.end(colour)
+        return
     for s in shards:
         s.ctx.colour_pass(colour, seed, sweep)
         s.pack(colour)
@@ -109,10 +169,24 @@ def colour_pass(shards: Sequence[Shard], transport, colour: int, seed: int, swee
         s.unpack(colour)
 
 
-def sweep(shards: Sequence[Shard], transport, seed: int, sweep_idx: int):
+def agree_halo_capacity(shards: Sequence[Shard], transport, grow: bool = True):
+    """The halo-row capacity (hence the record size) must be the same on every shard: the maximum of
+    what the shards have / ask for, set everywhere; records reallocated when it changed."""
+    want = 0
+    for s in shards:
+        cap, need = s.ctx.halo_capacity()
+        want = max(want, cap, need if grow else 0)
+    want = transport.allreduce_max(want) if hasattr(transport, "allreduce_max") else want
+    for s in shards:
+        s.ctx.halo_set_capacity(want)
+        s.ensure_records()
+
+
+def sweep(shards: Sequence[Shard], transport, seed: int, sweep_idx: int, overlap: bool = True):
     """SingleSiteSampler::single_iteration over all shards (3 colour passes)."""
     for colour in range(3):
-        colour_pass(shards, transport, colour, seed, sweep_idx)
+        colour_pass(shards, transport, colour, seed, sweep_idx, overlap)
+    agree_halo_capacity(shards, transport)
 
 
 def run_mcmc(shards: Sequence[Shard], transport, burn_in: int, batch: int, seed: int,
@@ -120,6 +194,7 @@ def run_mcmc(shards: Sequence[Shard], transport, burn_in: int, batch: int, seed:
     """SingleSiteSampler::run_mcmc (reference SingleSiteSampler.cpp:550-598) over shards.
     Returns batch-averaged J, D [n_nodes, 8] and the acceptance rate over all sites."""
     sw = first_sweep
+    agree_halo_capacity(shards, transport, grow=False)     # uploads size it per shard
     for _ in range(burn_in):
         sweep(shards, transport, seed, sw)
         sw += 1

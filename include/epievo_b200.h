@@ -5,7 +5,9 @@
  * harness call directly is listed beside each entry point ("replaces ..."), with
  * paths relative to the reference's src/libepievo/.  The C++ shim that keeps the
  * reference's class and function signatures on top of these calls is
- * epievo_b200/host/epievo_b200.hpp; INTEGRATION.md shows how a maintainer links it.
+ * epievo_b200/host/SingleSiteSampler.hpp (+ IndepSite_b200.cpp); INTEGRATION.md shows how a
+ * maintainer links it.  Precondition inherited from the reference's callers: SAMPLE_ROOT is false
+ * (SingleSiteSampler.cpp:441; the sampler's acceptance ratio relies on the root state being kept).
  *
  * Conventions
  *  - every call returns 0 on success, non-zero on failure; epv_last_error() then
@@ -156,6 +158,63 @@ int epv_accept_count(epv_ctx *ctx, int reset, uint64_t *n_accepted);
 int epv_halo_record_bytes(epv_ctx *ctx, uint64_t *bytes);
 int epv_halo_pack(epv_ctx *ctx, int colour, void *rec_lo, void *rec_hi);
 int epv_halo_unpack(epv_ctx *ctx, int colour, const void *rec_lo, const void *rec_hi);
+/* A halo row (and a record) holds up to `capacity` jumps per branch: sized from the rows next to the
+ * shard's ends at upload (at least 48, twice the largest), the same on every shard of a run -- the
+ * driver takes the maximum over shards and sets it everywhere.  *needed is what the boundary rows
+ * packed so far ask for (>= capacity when they passed half of it): call between sweeps and grow
+ * (contents are kept; epv_halo_record_bytes changes).  A row that still outgrows a record inside one
+ * sweep raises an error, it is never truncated. */
+int epv_halo_capacity(epv_ctx *ctx, uint64_t *capacity, uint64_t *needed);
+int epv_halo_set_capacity(epv_ctx *ctx, uint64_t capacity);
+
+/* The same colour pass with the exchange OVERLAPPED.  epv_pass_begin enqueues, on the context's side
+ * stream (epv_set_side_stream; default: an internal one), the halo-aware update of the few groups next
+ * to the shard's ends and the pack of the boundary sites' records (taken from the proposal staging,
+ * before the CSR is rebuilt) into rec_lo / rec_hi, and on the main stream the interior update and the
+ * CSR rebuild.  The driver moves the records ON THE SIDE STREAM (peer copy, NCCL send/recv) and calls
+ * epv_pass_end with the records received, which unpacks them on the side stream and makes the main
+ * stream's next work wait for that; after colour 2 it also does the per-sweep housekeeping (one host
+ * synchronisation).  Same chain, bit for bit, as epv_pass + epv_halo_pack/unpack. */
+int epv_set_side_stream(epv_ctx *ctx, void *cuda_stream);
+int epv_pass_begin(epv_ctx *ctx, int colour, uint64_t seed, uint64_t sweep_idx, void *rec_lo, void *rec_hi);
+int epv_pass_end(epv_ctx *ctx, int colour, const void *rec_lo, const void *rec_hi);
+/* epv_suffstats in two halves: enqueue the pass / read the result (so that a driver of several
+ * contexts has all of them running before it waits for the first). */
+int epv_suffstats_async(epv_ctx *ctx);
+int epv_suffstats_fetch(epv_ctx *ctx, double *J, double *D);
+
+/* ---- several GPUs behind one handle, one host process (csrc/api_multi.cu) --------------------------
+ * What the C++ drop-in uses when EPIEVO_B200_GPUS=N: the calls above with the same meaning and the
+ * same exchange format, over n_shards contexts holding contiguous site blocks (starts are multiples of
+ * 3), halo records moved by peer copies (NVLink) on the side streams, J/D sums added on the host.
+ * devices: n_shards CUDA ordinals, or NULL for 0..n_shards-1 (ordinals may repeat: several shards on
+ * one GPU, used by the tests).  n_shards = 1 is the single context.  The chain does not depend on the
+ * number of shards (Philox is keyed by the global site index). */
+typedef struct epv_multi epv_multi;
+int  epv_multi_create(epv_multi **m, int n_shards, const int *devices);
+void epv_multi_destroy(epv_multi *m);
+const char *epv_multi_last_error(const epv_multi *m);
+int  epv_multi_shards(const epv_multi *m);
+epv_ctx *epv_multi_context(epv_multi *m, int shard);
+int epv_multi_partition(uint64_t n_global, int n_shards, uint64_t *begin, uint64_t *end);
+int epv_multi_set_tree(epv_multi *m, uint64_t n_nodes, const uint64_t *subtree_sizes,
+                       const uint64_t *parent_ids, const double *branches);
+int epv_multi_set_model(epv_multi *m, const double *triplet_rates, const double *T);
+int epv_multi_upload_paths(epv_multi *m, uint64_t n_sites, uint64_t n_nodes, const uint8_t *init_state,
+                           const uint64_t *row_off, const double *jumps, const double *tot_time);
+int epv_multi_paths_size(epv_multi *m, uint64_t *n_sites, uint64_t *n_nodes, uint64_t *n_jumps);
+int epv_multi_download_paths(epv_multi *m, uint8_t *init_state, uint64_t *row_off, double *jumps,
+                             double *tot_time);
+int epv_multi_reset(epv_multi *m);
+int epv_multi_sweep(epv_multi *m, uint64_t seed, uint64_t sweep_idx, uint64_t *n_accepted);
+int epv_multi_run_mcmc(epv_multi *m, uint64_t burn_in, uint64_t batch, uint64_t seed, uint64_t first_sweep,
+                       double *J, double *D, double *acc_rate);
+int epv_multi_suffstats(epv_multi *m, double *J, double *D);
+int epv_multi_scale_jump_times(epv_multi *m, const double *new_branches);
+int epv_multi_mcem_iteration(epv_multi *m, uint64_t burn_in, uint64_t batch, uint64_t seed,
+                             uint64_t first_sweep, int optimize_branches, double param_tol, double *rates,
+                             double *T, double *branches, double *baseline, double *acc_rate, double *llh);
+uint64_t epv_multi_launch_count(const epv_multi *m);
 
 /* ---- deterministic per-site intermediates (parity tests of a2/a3/a4/a7) --------- */
 /* For local site `site`: the neighbour-interval lists of every node

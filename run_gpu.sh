@@ -1,15 +1,8 @@
-# One GPU-box session (round 2, session 1): the sampler-law evidence.
-# usage: gpurun --timeout 1500 -- 'bash run_gpu.sh'   (outputs land in gpurun_out/)
+# GPU-box session (round 2, session 3): multi-GPU handle + overlapped protocol on one GPU; ncu of the lockstep variant
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_gpu_exact_posterior.py tests/test_gpu_sampler.py -m gpu -q -s > gpurun_out/r02_pytest_law.log 2>&1; echo "pytest rc=$?" >> gpurun_out/r02_pytest_law.log
-tail -5 gpurun_out/r02_pytest_law.log
-for burn in 30 300; do
-  timeout 600 python tools/stats_probe.py --arm gpu --R 512 --burn $burn > gpurun_out/r02_stats_probe_bal8_R512_burn$burn.txt 2>&1
-  tail -3 gpurun_out/r02_stats_probe_bal8_R512_burn$burn.txt
-done
-# compute-sanitizer on the smoke path (memcheck, then racecheck): the colour classes' race freedom
-for tool in memcheck racecheck; do
-  timeout 600 compute-sanitizer --tool $tool --print-limit 20 python __graft_entry__.py --smoke > gpurun_out/r02_sanitizer_${tool}_smoke.txt 2>&1
-  echo "sanitizer $tool rc=$?" >> gpurun_out/r02_sanitizer_${tool}_smoke.txt
-  tail -4 gpurun_out/r02_sanitizer_${tool}_smoke.txt
-done
+timeout 900 python -m pytest tests/test_gpu_multi.py tests/test_gpu_sharded.py tests/test_gpu_chain_golden.py tests/test_gpu_compact.py tests/test_gpu_indep.py tests/test_gpu_dropin_cli.py tests/test_gpu_mcem.py -m gpu -x -q > gpurun_out/r02_pytest_s3.log 2>&1; echo "pytest rc=$?" >> gpurun_out/r02_pytest_s3.log
+tail -25 gpurun_out/r02_pytest_s3.log
+timeout 300 python bench.py --workload bal8 --no-cpu-baseline --no-mcem > gpurun_out/bench_s3_bal8.json 2> gpurun_out/bench_s3_bal8.err; tail -c 300 gpurun_out/bench_s3_bal8.json; echo
+B="python bench.py --steps 1 --warmup 1 --burn-in 1 --batch 1 --no-e2e --no-cpu-baseline --no-mcem"
+EPIEVO_B200_LIB=$PWD/epievo_b200/variants/libepievo_lock.so timeout 600 ncu --set full --clock-control none --import-source on -k regex:"mh_update" -s 6 -c 2 -o gpurun_out/prof_lock $B > gpurun_out/ncu_lock.log 2>&1
+tail -3 gpurun_out/ncu_lock.log

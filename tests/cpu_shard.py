@@ -74,6 +74,13 @@ class _CpuCtx:
     def download_paths(self):
         return self.o.store_paths()
 
+    # the stand-in's records are pickles of any size: nothing to agree on
+    def halo_capacity(self):
+        return 48, 0
+
+    def halo_set_capacity(self, capacity):
+        pass
+
 
 class CpuShard:
     def __init__(self, tree, rates, T, n_global, world, rank):
@@ -83,6 +90,18 @@ class CpuShard:
                            self.halo_lo, self.halo_hi)
         mk = lambda: torch.zeros(REC_BYTES, dtype=torch.uint8)
         self.send_lo, self.send_hi, self.recv_lo, self.recv_hi = mk(), mk(), mk(), mk()
+        self.side, self.device = None, torch.device("cpu")
+
+    def ensure_records(self):
+        pass
+
+    # epv_pass_begin / epv_pass_end: update + pack, then unpack (no streams to overlap on the CPU)
+    def begin(self, colour, seed, sweep):
+        self.ctx.colour_pass(colour, seed, sweep)
+        self.pack(colour)
+
+    def end(self, colour):
+        self.unpack(colour)
 
     # the same site arithmetic as csrc/api_halo.cu
     def _pack_sites(self, colour):
