@@ -45,6 +45,7 @@ SIGNATURES = {
                                      dp, dp]),
     "epv_simulate": (C.c_int, [ctx_p, u64, u8p, u64, u64p]),
     "epv_simulate_fetch": (C.c_int, [ctx_p, u8p, u64p, dp]),
+    "epv_simulate_adopt": (C.c_int, [ctx_p]),
     "epv_pass": (C.c_int, [ctx_p, C.c_int, u64, u64]),
     "epv_accept_count": (C.c_int, [ctx_p, C.c_int, u64p]),
     "epv_halo_record_bytes": (C.c_int, [ctx_p, u64p]),
@@ -55,6 +56,12 @@ SIGNATURES = {
     "epv_set_side_stream": (C.c_int, [ctx_p, C.c_void_p]),
     "epv_pass_begin": (C.c_int, [ctx_p, C.c_int, u64, u64, C.c_void_p, C.c_void_p]),
     "epv_pass_end": (C.c_int, [ctx_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "epv_stats_words": (C.c_int, [ctx_p, u64p]),
+    "epv_stats_begin": (C.c_int, [ctx_p]),
+    "epv_stats_accumulate": (C.c_int, [ctx_p]),
+    "epv_stats_export": (C.c_int, [ctx_p, C.c_void_p]),
+    "epv_stats_add": (C.c_int, [ctx_p, C.c_void_p]),
+    "epv_stats_fold": (C.c_int, [ctx_p, C.c_void_p, dp, dp]),
     "epv_suffstats_async": (C.c_int, [ctx_p]),
     "epv_suffstats_fetch": (C.c_int, [ctx_p, dp, dp]),
     "epv_multi_create": (C.c_int, [C.POINTER(ctx_p), C.c_int, C.POINTER(C.c_int)]),

@@ -37,6 +37,8 @@ struct epv_multi {
   std::vector<void *> recv_lo[2], recv_hi[2];
   std::vector<cudaEvent_t> ev_sent;
   int parity = 0;
+  void *stats_stage = nullptr;                // on shard 0's GPU: a peer's J/D accumulators in transit
+  uint64_t stats_words = 0;
   std::string error;
 };
 
@@ -116,6 +118,30 @@ int multi_pass(epv_multi *m, int colour, uint64_t seed, uint64_t sweep) {
   return 0;
 }
 
+// J/D over all shards, exactly: every shard's integer accumulators are copied to shard 0's GPU and added
+// there, then folded once -- the result does not depend on the number of shards.
+int multi_fold_stats(epv_multi *m, double *J, double *D) {
+  epv_ctx *c0 = m->ctx[0];
+  uint64_t words = 0;
+  MCK(m, 0, epv_stats_words(c0, &words));
+  cudaSetDevice(m->dev[0]);
+  if (words != m->stats_words) {
+    cudaFree(m->stats_stage); m->stats_stage = nullptr;
+    MCUDA(m, cudaMalloc(&m->stats_stage, words*8));
+    m->stats_words = words;
+  }
+  for (int r = 1; r < m->n; ++r) {
+    cudaSetDevice(m->dev[r]);
+    MCUDA(m, cudaEventRecord(m->ev_sent[r], m->ctx[r]->stream));          // shard r's passes are enqueued
+    cudaSetDevice(m->dev[0]);
+    MCUDA(m, cudaStreamWaitEvent(c0->stream, m->ev_sent[r], 0));
+    if (m->dev[r] == m->dev[0]) MCUDA(m, cudaMemcpyAsync(m->stats_stage, m->ctx[r]->d_ss, words*8, cudaMemcpyDeviceToDevice, c0->stream));
+    else MCUDA(m, cudaMemcpyPeerAsync(m->stats_stage, m->dev[0], m->ctx[r]->d_ss, m->dev[r], words*8, c0->stream));
+    MCK(m, 0, epv_stats_add(c0, m->stats_stage));
+  }
+  return mctx(m, 0, epv_stats_fold(c0, nullptr, J, D));
+}
+
 int multi_sweep(epv_multi *m, uint64_t seed, uint64_t sweep) {
   if (m->n == 1) return mctx(m, 0, epv_sweep(m->ctx[0], seed, sweep, nullptr));
   for (int colour = 0; colour < 3; ++colour)
@@ -182,6 +208,7 @@ void epv_multi_destroy(epv_multi *m) {
   if (!m) return;
   for (int r = 0; r < m->n; ++r) if (m->ctx[r]) epv_synchronize(m->ctx[r]);
   free_records(m);
+  if (m->stats_stage) { cudaSetDevice(m->dev[0]); cudaFree(m->stats_stage); }
   for (int r = 0; r < m->n; ++r) {
     if (m->ev_sent[r]) { cudaSetDevice(m->dev[r]); cudaEventDestroy(m->ev_sent[r]); }
     epv_destroy(m->ctx[r]);
@@ -323,14 +350,9 @@ int epv_multi_sweep(epv_multi *m, uint64_t seed, uint64_t sweep_idx, uint64_t *n
 
 int epv_multi_suffstats(epv_multi *m, double *J, double *D) {
   if (!m) return 1;
-  const size_t k = (size_t)m->n_nodes*8;
-  std::vector<double> j(k), d(k);
-  std::fill(J, J + k, 0.0); std::fill(D, D + k, 0.0);
-  for (int r = 0; r < m->n; ++r) {
-    MCK(m, r, epv_suffstats(m->ctx[r], j.data(), d.data()));
-    for (size_t i = 0; i < k; ++i) { J[i] += j[i]; D[i] += d[i]; }
-  }
-  return 0;
+  if (m->n == 1) return mctx(m, 0, epv_suffstats(m->ctx[0], J, D));
+  for (int r = 0; r < m->n; ++r) { MCK(m, r, epv_stats_begin(m->ctx[r])); MCK(m, r, epv_stats_accumulate(m->ctx[r])); }
+  return multi_fold_stats(m, J, D);
 }
 
 int epv_multi_run_mcmc(epv_multi *m, uint64_t burn_in, uint64_t batch, uint64_t seed, uint64_t first_sweep,
@@ -343,17 +365,12 @@ int epv_multi_run_mcmc(epv_multi *m, uint64_t burn_in, uint64_t batch, uint64_t 
   for (uint64_t i = 0; i < burn_in; ++i, ++sweep)            // SingleSiteSampler.cpp:560-561
     if (int rc = multi_sweep(m, seed, sweep)) return rc;
   for (int r = 0; r < m->n; ++r) MCK(m, r, epv_accept_count(m->ctx[r], 1, nullptr));
-  std::fill(J, J + k, 0.0); std::fill(D, D + k, 0.0);
-  std::vector<double> j(k), d(k);
+  for (int r = 0; r < m->n; ++r) MCK(m, r, epv_stats_begin(m->ctx[r]));
   for (uint64_t i = 0; i < batch; ++i, ++sweep) {            // :576-587
     if (int rc = multi_sweep(m, seed, sweep)) return rc;
-    // every shard's J/D pass is enqueued before the first result is read back
-    for (int r = 0; r < m->n; ++r) MCK(m, r, epv_suffstats_async(m->ctx[r]));
-    for (int r = 0; r < m->n; ++r) {
-      MCK(m, r, epv_suffstats_fetch(m->ctx[r], j.data(), d.data()));
-      for (size_t x = 0; x < k; ++x) { J[x] += j[x]; D[x] += d[x]; }
-    }
+    for (int r = 0; r < m->n; ++r) MCK(m, r, epv_stats_accumulate(m->ctx[r]));     // enqueued only
   }
+  if (int rc = multi_fold_stats(m, J, D)) return rc;
   uint64_t acc = 0;
   for (int r = 0; r < m->n; ++r) { uint64_t a = 0; MCK(m, r, epv_accept_count(m->ctx[r], 1, &a)); acc += a; }
   for (size_t x = 0; x < k; ++x) { J[x] /= (double)batch; D[x] /= (double)batch; }      // :590-594

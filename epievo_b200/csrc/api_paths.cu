@@ -120,7 +120,7 @@ int set_halo_capacity(epv_ctx *c, int k) {
 }
 
 // Local site of halo slot k (0..2 low halo, 3..5 high halo), or -1 if the slot is unused.
-static int64_t slot_site(const epv_ctx *c, int k) {
+int64_t slot_site(const epv_ctx *c, int k) {
   if (k < HALO_W) return (uint64_t)k < c->halo_lo ? k : -1;
   return (uint64_t)(k - HALO_W) < c->halo_hi ? (int64_t)(c->n_sites - c->halo_hi) + (k - HALO_W) : -1;
 }
@@ -130,7 +130,7 @@ static int64_t slot_site(const epv_ctx *c, int k) {
 namespace epv {
 
 // Argument checks shared by the two upload entry points; fills in the default shard.
-static int check_upload(epv_ctx *c, uint64_t n_sites, uint64_t n_nodes, const double *tot_time) {
+int check_upload(epv_ctx *c, uint64_t n_sites, uint64_t n_nodes, const double *tot_time) {
   if (!c->n_nodes) return fail(c, "epv_set_tree must be called before epv_upload_paths");
   if ((int)n_nodes != c->n_nodes) return fail(c, "paths and tree disagree on the number of nodes");
   if (n_sites < 3) return fail(c, "need at least 3 sites");
@@ -152,7 +152,7 @@ static int check_upload(epv_ctx *c, uint64_t n_sites, uint64_t n_nodes, const do
 
 // Everything whose size depends only on (n_sites, n_nodes); kept across uploads of the
 // same shape.
-static int ensure_shape(epv_ctx *c, uint64_t n_sites) {
+int ensure_shape(epv_ctx *c, uint64_t n_sites) {
   if (c->n_sites == n_sites && c->d_off[0]) return 0;
   free_paths(c);
   c->h_jcap.clear();
@@ -181,7 +181,7 @@ static int ensure_shape(epv_ctx *c, uint64_t n_sites) {
 }
 
 // Jump buffers (+ the proposal staging blob): reallocated only when a branch no longer fits.
-static int ensure_jumps(epv_ctx *c, const std::vector<uint64_t> &count) {
+int ensure_jumps(epv_ctx *c, const std::vector<uint64_t> &count) {
   const int n_br = c->n_nodes - 1;
   uint64_t sum = 0;
   for (int bi = 0; bi < n_br; ++bi) sum += count[bi];

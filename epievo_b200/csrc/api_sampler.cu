@@ -149,11 +149,11 @@ int read_accepts(epv_ctx *c, uint64_t *n) {
   return 0;
 }
 
-int do_suffstats(epv_ctx *c) {
+int do_suffstats(epv_ctx *c, bool clear = true, bool fold = true) {
   uint64_t lo, hi; interior(c, lo, hi);
   c->launches += launch_suffstats(c->view(c->cur), c->d_state, c->W, c->tree(), c->n_sites, lo, hi,
-                                  c->d_J, c->d_D, c->d_ss, c->stream, c->sm_count);
-  c->stats_valid = true;
+                                  c->d_J, c->d_D, c->d_ss, c->stream, c->sm_count, clear, fold);
+  c->stats_valid = fold;
   return 0;
 }
 
@@ -195,15 +195,17 @@ int epv_run_mcmc_raw(epv_ctx *c, uint64_t burn_in, uint64_t batch, uint64_t seed
     if (int r = housekeeping(c)) return r;
   }
   EPV_CUDA(c, cudaMemsetAsync(c->d_nacc, 0, sizeof(unsigned long long), c->stream));
-  EPV_CUDA(c, cudaMemsetAsync(c->d_Jsum, 0, nb, c->stream));
-  EPV_CUDA(c, cudaMemsetAsync(c->d_Dsum, 0, nb, c->stream));
+  // the batch's J/D passes add into ONE set of integer accumulators, folded once: the sums over the
+  // batch are exact, and the same whatever the number of shards (epv_multi_run_mcmc adds the shards'
+  // accumulators before the fold)
+  EPV_CUDA(c, cudaMemsetAsync(c->d_ss, 0, suffstats_scratch_bytes(c->n_nodes, c->sm_count), c->stream));
   for (uint64_t i = 0; i < batch; ++i, ++sweep) {            // :576-587
     if (int r = one_sweep(c, seed, sweep)) return r;
     if (int r = housekeeping(c)) return r;
-    if (int r = do_suffstats(c)) return r;
-    launch_axpy_stats(c->d_Jsum, c->d_Dsum, c->d_J, c->d_D, c->n_nodes*8, c->stream);
-    ++c->launches;
+    if (int r = do_suffstats(c, false, false)) return r;
   }
+  launch_suffstats_fold(c->d_ss, c->tree(), c->d_Jsum, c->d_Dsum, c->stream);
+  ++c->launches;
   EPV_CUDA(c, cudaMemcpyAsync(J_sum, c->d_Jsum, nb, cudaMemcpyDeviceToHost, c->stream));
   EPV_CUDA(c, cudaMemcpyAsync(D_sum, c->d_Dsum, nb, cudaMemcpyDeviceToHost, c->stream));
   uint64_t n = 0;
@@ -232,6 +234,65 @@ int epv_suffstats(epv_ctx *c, double *J, double *D) {
   const size_t nb = (size_t)c->n_nodes*8*sizeof(double);
   EPV_CUDA(c, cudaMemcpyAsync(J, c->d_J, nb, cudaMemcpyDeviceToHost, c->stream));
   EPV_CUDA(c, cudaMemcpyAsync(D, c->d_D, nb, cudaMemcpyDeviceToHost, c->stream));
+  EPV_CUDA(c, cudaStreamSynchronize(c->stream));
+  EPV_CUDA(c, cudaGetLastError());
+  return 0;
+}
+
+/* J/D statistics as exact integer accumulators, for drivers of several shards: epv_stats_begin clears
+ * them, epv_stats_accumulate adds one J/D pass over the current paths (enqueued only), epv_stats_export
+ * copies them (epv_stats_words 8-byte words) to a DEVICE buffer of the caller, which adds the shards'
+ * buffers element-wise as 64-bit integers (peer copies + epv_stats_add, or an NCCL all-reduce on int64),
+ * and epv_stats_fold turns a summed buffer (NULL: the context's own) into J / D [n_nodes*8].  Integer
+ * sums are exact, so J and D do not depend on how the sites were sharded. */
+int epv_stats_words(epv_ctx *c, uint64_t *words) {
+  if (!c || !words) return 1;
+  if (!c->n_nodes) return fail(c, "epv_set_tree must be called first");
+  *words = suffstats_scratch_bytes(c->n_nodes, c->sm_count)/8;
+  return 0;
+}
+
+int epv_stats_begin(epv_ctx *c) {
+  if (!c) return 1;
+  if (!c->n_sites) return fail(c, "no paths loaded");
+  cudaSetDevice(c->device);
+  EPV_CUDA(c, cudaMemsetAsync(c->d_ss, 0, suffstats_scratch_bytes(c->n_nodes, c->sm_count), c->stream));
+  c->stats_valid = false;
+  return 0;
+}
+
+int epv_stats_accumulate(epv_ctx *c) {
+  if (!c) return 1;
+  if (!c->n_sites) return fail(c, "no paths loaded");
+  cudaSetDevice(c->device);
+  return do_suffstats(c, false, false);
+}
+
+int epv_stats_export(epv_ctx *c, void *dev_words) {
+  if (!c || !dev_words) return 1;
+  cudaSetDevice(c->device);
+  EPV_CUDA(c, cudaMemcpyAsync(dev_words, c->d_ss, suffstats_scratch_bytes(c->n_nodes, c->sm_count),
+                              cudaMemcpyDeviceToDevice, c->stream));
+  return 0;
+}
+
+int epv_stats_add(epv_ctx *c, const void *dev_words) {
+  if (!c || !dev_words) return 1;
+  cudaSetDevice(c->device);
+  launch_suffstats_add(c->d_ss, static_cast<const unsigned long long *>(dev_words), c->n_nodes, c->stream);
+  ++c->launches;
+  return 0;
+}
+
+int epv_stats_fold(epv_ctx *c, const void *dev_words, double *J, double *D) {
+  if (!c) return 1;
+  cudaSetDevice(c->device);
+  const unsigned long long *src = dev_words ? static_cast<const unsigned long long *>(dev_words) : c->d_ss;
+  launch_suffstats_fold(src, c->tree(), c->d_Jsum, c->d_Dsum, c->stream);
+  ++c->launches;
+  const size_t nb = (size_t)c->n_nodes*8*sizeof(double);
+  EPV_CUDA(c, cudaMemcpyAsync(J, c->d_Jsum, nb, cudaMemcpyDeviceToHost, c->stream));
+  EPV_CUDA(c, cudaMemcpyAsync(D, c->d_Dsum, nb, cudaMemcpyDeviceToHost, c->stream));
   EPV_CUDA(c, cudaStreamSynchronize(c->stream));
   EPV_CUDA(c, cudaGetLastError());
   return 0;

@@ -369,4 +369,64 @@ int epv_simulate_fetch(epv_ctx *c, uint8_t *init_state, uint64_t *row_off, doubl
   return 0;
 }
 
+/* The simulated histories become the context's paths WITHOUT leaving the device (for shards too
+ * large to stage through host arrays: 10^7 sites x 62 branches is 6 GB of offsets alone).  Same
+ * result as epv_simulate_fetch + epv_upload_paths. */
+int epv_simulate_adopt(epv_ctx *c) {
+  if (!c) return 1;
+  SimResult &res = result_of(c);
+  if (!res.n_sites) return fail(c, "epv_simulate_adopt needs a preceding epv_simulate");
+  const uint64_t n = res.n_sites;
+  if (int r = check_upload(c, n, (uint64_t)res.n_nodes, c->h_branch.data())) return r;
+  const int n_br = c->n_nodes - 1;
+  const uint64_t own_lo = c->halo_lo, own_hi = n - c->halo_hi, n_own = own_hi - own_lo;
+  // where every branch's owned rows start and end in the simulator's jump array
+  std::vector<unsigned long long> lo(n_br), hi(n_br);
+  EPV_CUDA(c, cudaMemcpy2D(lo.data(), 8, res.off + n + own_lo, n*8, 8, (size_t)n_br, cudaMemcpyDeviceToHost));
+  EPV_CUDA(c, cudaMemcpy2D(hi.data(), 8, res.off + n + own_hi, n*8, 8, (size_t)n_br, cudaMemcpyDeviceToHost));
+  std::vector<uint64_t> count(n_br);
+  for (int bi = 0; bi < n_br; ++bi) count[bi] = hi[bi] - lo[bi];
+  EPV_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (int r = ensure_shape(c, n)) return r;
+  if (int r = ensure_jumps(c, count)) return r;
+  c->cur = 0; c->tri_valid = false; c->stats_valid = false;
+  launch_import(res.init, res.off, n, c->n_nodes, own_lo, n_own, c->d_off[0], c->off_pitch, c->d_state, c->W, c->stream);
+  ++c->launches;
+  for (int bi = 0; bi < n_br; ++bi)
+    if (count[bi])
+      EPV_CUDA(c, cudaMemcpyAsync(c->d_jmp[0] + c->h_jbase[bi], res.jumps + lo[bi], count[bi]*sizeof(double),
+                                  cudaMemcpyDeviceToDevice, c->stream));
+  // halo rows (<= 6 sites): offsets and jump times through the host into the halo store
+  if (c->halo_lo || c->halo_hi) {
+    std::vector<unsigned long long> ho((size_t)2*HALO_W*n_br*2, 0);
+    uint64_t kmax = 0;
+    for (int k = 0; k < 2*HALO_W; ++k) {
+      const int64_t s = slot_site(c, k);
+      if (s < 0) continue;
+      EPV_CUDA(c, cudaMemcpy2D(&ho[(size_t)k*n_br*2], 16, res.off + n + (uint64_t)s, n*8, 16, (size_t)n_br, cudaMemcpyDeviceToHost));
+      for (int bi = 0; bi < n_br; ++bi) kmax = std::max<uint64_t>(kmax, ho[((size_t)k*n_br + bi)*2 + 1] - ho[((size_t)k*n_br + bi)*2]);
+    }
+    // the owned rows next to the ends count too (they are the ones packed later)
+    if (kmax > 30000) return fail(c, "a shard-boundary row holds more than 30000 jumps");
+    if (int r = set_halo_capacity(c, std::max<int>(HALO_K_MIN, 2*(int)kmax + 16))) return r;
+    const size_t HK = c->halo_k;
+    std::vector<uint16_t> hc((size_t)2*HALO_W*n_br, 0);
+    std::vector<double> hj((size_t)2*HALO_W*n_br*HK, 0.0);
+    for (int k = 0; k < 2*HALO_W; ++k) {
+      if (slot_site(c, k) < 0) continue;
+      for (int bi = 0; bi < n_br; ++bi) {
+        const unsigned long long a = ho[((size_t)k*n_br + bi)*2], b = ho[((size_t)k*n_br + bi)*2 + 1];
+        hc[(size_t)k*n_br + bi] = (uint16_t)(b - a);
+        if (b > a) EPV_CUDA(c, cudaMemcpy(&hj[((size_t)k*n_br + bi)*HK], res.jumps + a, (b - a)*sizeof(double), cudaMemcpyDeviceToHost));
+      }
+    }
+    EPV_CUDA(c, cudaMemcpyAsync(c->d_hcnt, hc.data(), hc.size()*sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream));
+    EPV_CUDA(c, cudaMemcpyAsync(c->d_hjmp, hj.data(), hj.size()*sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  }
+  EPV_CUDA(c, cudaStreamSynchronize(c->stream));
+  EPV_CUDA(c, cudaGetLastError());
+  res.release();
+  return 0;
+}
+
 }  // extern "C"

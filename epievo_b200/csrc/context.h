@@ -111,6 +111,11 @@ int check_cuda(epv_ctx *c, cudaError_t e, const char *what);
 void free_paths(epv_ctx *c);
 int check_device_flags(epv_ctx *c);
 int set_halo_capacity(epv_ctx *c, int k);  // reallocates the halo store (contents kept)
+// pieces of the upload path shared with epv_simulate_adopt (api_paths.cu)
+int64_t slot_site(const epv_ctx *c, int k);
+int check_upload(epv_ctx *c, uint64_t n_sites, uint64_t n_nodes, const double *tot_time);
+int ensure_shape(epv_ctx *c, uint64_t n_sites);
+int ensure_jumps(epv_ctx *c, const std::vector<uint64_t> &count);
 void sim_release(epv_ctx *c);          // frees what epv_simulate left on the device   // reads d_err, turns sticky flags into an error
 }
 #define EPV_CUDA(c, call) do { if (int _r = epv::check_cuda((c), (call), #call)) return _r; } while (0)

@@ -78,7 +78,10 @@ void launch_end_cond(double r0, double r1, int a, int b, double T, uint64_t seed
 // (8 D sums, 8 J counts, 8 event-free row counts are folded on device).
 int launch_suffstats(const PathView &pv, const uint8_t *state, int W, const TreeDev &tree,
                      uint64_t n_sites, uint64_t lo, uint64_t hi, double *J, double *D,
-                     unsigned long long *scratch, cudaStream_t st, int sm_count);   // returns kernels launched
+                     unsigned long long *scratch, cudaStream_t st, int sm_count, bool clear = true,
+                     bool fold = true);   // returns kernels launched
+void launch_suffstats_fold(const unsigned long long *scratch, const TreeDev &tree, double *J, double *D, cudaStream_t st);
+void launch_suffstats_add(unsigned long long *dst, const unsigned long long *src, int n_nodes, cudaStream_t st);
 size_t suffstats_scratch_bytes(int n_nodes, int sm_count);
 void launch_llh_grad(const double *J, const double *D, int n_nodes, const double *rates_dev,
                      double *out9, cudaStream_t st);

@@ -18,10 +18,12 @@
 // the slowest earlier tile (update time varies with the rows' jump counts).  Splitting
 // costs one staging round trip of the accepted proposals (a few % of the row bytes).
 #include <cstdlib>
+#include <type_traits>
 
 #include "kernels.h"
 #include "mh_flat.cuh"
 #include "mh_lock.cuh"
+#include "mh_mix.cuh"
 #include "scan.cuh"
 
 namespace epv {
@@ -52,10 +54,13 @@ __host__ __device__ constexpr int mh_minblocks(int maxn) { return maxn <= 16 ? 4
 // tree), 0.44 vs 0.41 (1e6-site single branch) -- the interval loop of the lanes that do have neighbour
 // jumps runs per BRANCH (max over lanes of the branch's intervals, ~2.2 heavy iterations per branch at 2-4
 // active lanes) instead of once per site.  Kept behind EPV_MH_LOCK as the base of the next step.
-#ifndef EPV_MH_LOCK
-#define EPV_MH_LOCK 0
+// EPV_MH_IMPL: 0 = mh_site_flat, 1 = mh_site_lock, 2 = mh_site_mix (mh_mix.cuh: lockstep for the
+// single-interval branches, per-lane flat loops for the others); trees wider than 64 nodes always 0.
+#ifndef EPV_MH_IMPL
+#define EPV_MH_IMPL 2
 #endif
-__host__ __device__ constexpr bool mh_lock(int maxn) { return EPV_MH_LOCK && maxn <= 64; }
+__host__ __device__ constexpr int mh_impl(int maxn) { return maxn <= 64 ? EPV_MH_IMPL : 0; }
+__host__ __device__ constexpr bool mh_lock(int maxn) { return mh_impl(maxn) != 0; }
 
 // jump-queue slots per thread (shared memory: 24 B each)
 __host__ __device__ constexpr int mh_qcap(int maxn) { return maxn <= 16 ? 8 : maxn <= 64 ? 16 : 24; }
@@ -73,10 +78,10 @@ __host__ __device__ constexpr int mh_qcap(int maxn) { return maxn <= 16 ? 8 : ma
 // [MH_THREADS] int, then (lockstep routine, trees up to 64 nodes) TreeTab [n_nodes], BranchTab [n_nodes],
 // jump counts per node u16 [n_nodes][MH_THREADS], q of the internal nodes f64 [2*slots][MH_THREADS].
 struct MhShared {
-  QSlot *queue; int *excl; TreeTab *tt; BranchTab *bt; uint16_t *pn; double *q;
+  QSlot *queue; int *excl; TreeTab *tt; BranchTab *bt; uint16_t *pn; double *q; uint16_t *poff;
 };
 template <int MAXN>
-__host__ __device__ inline size_t mh_smem_layout(int n_nodes, int q_slots, size_t *off /*[6]*/) {
+__host__ __device__ inline size_t mh_smem_layout(int n_nodes, int q_slots, size_t *off /*[7]*/) {
   size_t at = 0;
   off[0] = at; at += (size_t)MH_THREADS*mh_qcap(MAXN)*sizeof(QSlot);
   off[1] = at; at += (size_t)MH_THREADS*sizeof(int);
@@ -87,8 +92,9 @@ __host__ __device__ inline size_t mh_smem_layout(int n_nodes, int q_slots, size_
     off[4] = at; at += (size_t)n_nodes*MH_THREADS*sizeof(uint16_t);
     at = (at + 15) & ~(size_t)15;
     off[5] = at; at += (size_t)2*q_slots*MH_THREADS*sizeof(double);
+    off[6] = at; if (mh_impl(MAXN) == 2) at += (size_t)n_nodes*MH_THREADS*sizeof(uint16_t);
   }
-  else off[2] = off[3] = off[4] = off[5] = at;
+  else off[2] = off[3] = off[4] = off[5] = off[6] = at;
   return at;
 }
 
@@ -113,13 +119,21 @@ mh_update_group(const PassArgs &a, const ModelParams &s_mp, const CtxTables &s_t
   const bool active = g < a.n_groups && st >= a.upd_lo && st < a.upd_hi && gsite >= 1 &&
                       gsite + 1 < (int64_t)a.n_global;
   SiteCtx c; c.pv = a.in; c.state = a.state; c.W = a.W; c.tree = a.tree; c.site = st;
+  constexpr bool MIX = mh_impl(MAXN) == 2;
   if constexpr (LOCK) {
-    LockScratch<MAXN, PB, QCAP, QSMEM> S;
+    typename std::conditional<MIX, MixScratch<MAXN, PB, QCAP, QSMEM>, LockScratch<MAXN, PB, QCAP, QSMEM> >::type S;
     S.queue = sh.queue + t*QCAP; S.excl = sh.excl + (t & ~31);
     S.pn_s = sh.pn + t; S.q_s = sh.q + t;
-    int r = mh_site_lock<MAXN, PB, QCAP, HALO, QSMEM>(active, a.coop != 0, s_mp, s_tb, sh.tt, sh.bt, c, a.state, a.tri_llh,
-                                                      a.seed, a.sweep, (uint64_t)gsite, a.n_global, S, pj_local, MAXJ,
-                                                      pend_bits, propmask, total);
+    if constexpr (MIX) S.poff_s = sh.poff + t;
+    auto site_update = [&](bool act, double *pj, int cap, auto &pe, auto &pm, int &tot) {
+      if constexpr (MIX)
+        return mh_site_mix<MAXN, PB, QCAP, HALO, QSMEM>(act, a.coop != 0, s_mp, s_tb, sh.tt, sh.bt, c, a.state, a.tri_llh,
+                                                        a.seed, a.sweep, (uint64_t)gsite, a.n_global, S, pj, cap, pe, pm, tot);
+      else
+        return mh_site_lock<MAXN, PB, QCAP, HALO, QSMEM>(act, a.coop != 0, s_mp, s_tb, sh.tt, sh.bt, c, a.state, a.tri_llh,
+                                                         a.seed, a.sweep, (uint64_t)gsite, a.n_global, S, pj, cap, pe, pm, tot);
+    };
+    int r = site_update(active, pj_local, MAXJ, pend_bits, propmask, total);
     if (DEFER) {
       if (r == -1 || r == -3) {
         a.ovf_list[1 + atomicAdd(a.ovf_list, 1u)] = (uint32_t)g;
@@ -147,9 +161,7 @@ mh_update_group(const PassArgs &a, const ModelParams &s_mp, const CtxTables &s_t
         }
         const bool redo = again && r == -1;
         typename LockMask<MAXN>::type pm2 = 0, pe2 = 0; int tot2 = 0;
-        const int r2 = mh_site_lock<MAXN, PB, QCAP, HALO, QSMEM>(redo && !generic, a.coop != 0, s_mp, s_tb, sh.tt, sh.bt, c,
-                                                                 a.state, a.tri_llh, a.seed, a.sweep, (uint64_t)gsite,
-                                                                 a.n_global, S, pr.pj, pr.cap, pe2, pm2, tot2);
+        const int r2 = site_update(redo && !generic, pr.pj, pr.cap, pe2, pm2, tot2);
         if (redo && !generic) { r = r2; propmask = pm2; pend_bits = pe2; total = tot2; }
         if (redo && generic)
           r = mh_site(s_mp, c, a.state, a.tri_llh, a.seed, a.sweep, (uint64_t)gsite, a.n_global,
@@ -205,12 +217,17 @@ mh_update_group(const PassArgs &a, const ModelParams &s_mp, const CtxTables &s_t
         so = (uint32_t)at;
         double *blob = a.stage + at;
         uint16_t *cnt = reinterpret_cast<uint16_t *>(blob);
+        int k = 0;
         for (int bi = 0; bi < 4*hw; ++bi) {
           uint16_t n = 0;
           if (bi < n_br) n = local_pn ? pn[bi + 1] : (((propmask >> (bi + 1)) & 1) ? sh.pn[(bi + 1)*MH_THREADS + t] : 0);
           cnt[bi] = n;
+          if (MIX && !local_pn && n) {                 // rows are not in branch order in pj: gather
+            const double *src = pr.pj + sh.poff[(bi + 1)*MH_THREADS + t];
+            for (int x = 0; x < n; ++x) blob[hw + k++] = src[x];
+          }
         }
-        for (int k = 0; k < total; ++k) blob[hw + k] = pr.pj[k];
+        if (!MIX || local_pn) for (k = 0; k < total; ++k) blob[hw + k] = pr.pj[k];
       }
     }
   }
@@ -232,11 +249,12 @@ mh_update_kernel(const PassArgs a, int q_slots) {
   fill_tables(a.mp, s_tb, t);
   MhShared sh;
   {
-    size_t off[6];
+    size_t off[7];
     mh_smem_layout<MAXN>(a.tree.n_nodes, q_slots, off);
     sh.queue = reinterpret_cast<QSlot *>(s_dyn + off[0]); sh.excl = reinterpret_cast<int *>(s_dyn + off[1]);
     sh.tt = reinterpret_cast<TreeTab *>(s_dyn + off[2]); sh.bt = reinterpret_cast<BranchTab *>(s_dyn + off[3]);
     sh.pn = reinterpret_cast<uint16_t *>(s_dyn + off[4]); sh.q = reinterpret_cast<double *>(s_dyn + off[5]);
+    sh.poff = reinterpret_cast<uint16_t *>(s_dyn + off[6]);
   }
   __syncthreads();
   if (mh_lock(MAXN)) {
@@ -455,7 +473,7 @@ static size_t smem_budget() { return (size_t)(232448 - 1024*mh_minblocks(MAXN))/
 template <int MAXN, int MAXJ, bool HALO, bool DEFER>
 static void
 launch_variant(const PassArgs &a, unsigned blocks, cudaStream_t st) {
-  size_t off[6];
+  size_t off[7];
   const bool qsmem = mh_lock(MAXN) && mh_smem_layout<MAXN>(a.tree.n_nodes, a.q_slots, off) <= smem_budget<MAXN>();
   if (qsmem) {
     const size_t smem = mh_smem_layout<MAXN>(a.tree.n_nodes, a.q_slots, off);

@@ -601,14 +601,33 @@ launch_suffstats_generic(const PathView &pv, const uint8_t *state, int W, int n_
 
 }  // namespace
 
+__global__ void
+acc_add_kernel(unsigned long long *dst, const unsigned long long *src, int n) {
+  const int i = blockIdx.x*blockDim.x + threadIdx.x;
+  if (i < n) dst[i] += src[i];
+}
+
+void
+launch_suffstats_fold(const unsigned long long *scratch, const TreeDev &tree, double *J, double *D, cudaStream_t st) {
+  suffstats_fold_kernel<<<(tree.n_nodes*8 + 127)/128, 128, 0, st>>>(scratch, tree.branch, tree.n_nodes, J, D);
+}
+
+void
+launch_suffstats_add(unsigned long long *dst, const unsigned long long *src, int n_nodes, cudaStream_t st) {
+  const int n = (n_nodes - 1)*SS_ACC;
+  acc_add_kernel<<<(n + 127)/128, 128, 0, st>>>(dst, src, n);
+}
+
+// The integer accumulators of the pass are ADDED to scratch (cleared first when clear is set); fold turns
+// them into J / D.  All-integer => sums over passes and over shards are exact and order-independent.
 // Returns the number of kernels launched.
 int
 launch_suffstats(const PathView &pv, const uint8_t *state, int W, const TreeDev &tree,
                  uint64_t, uint64_t lo, uint64_t hi, double *J, double *D,
-                 unsigned long long *scratch, cudaStream_t st, int sm_count) {
+                 unsigned long long *scratch, cudaStream_t st, int sm_count, bool clear, bool fold) {
   const int n_br = tree.n_nodes - 1;
-  int launches = 1;
-  cudaMemsetAsync(scratch, 0, (size_t)n_br*SS_ACC*8, st);
+  int launches = fold ? 1 : 0;
+  if (clear) cudaMemsetAsync(scratch, 0, (size_t)n_br*SS_ACC*8, st);
   if (hi > lo) {
     // rows [r0, r0 + 128 n_tiles): interior sites whose neighbours are owned, offsets r0-1 ..
     // r0 + 128 n_tiles + 1 inside the CSR; the remainder on either side goes to the generic kernel
@@ -641,8 +660,7 @@ launch_suffstats(const PathView &pv, const uint8_t *state, int W, const TreeDev 
       if (hi > t_hi) { launch_suffstats_generic(pv, state, W, n_br, tree.branch, t_hi, hi, scratch, st, sm_count); ++launches; }
     }
   }
-  suffstats_fold_kernel<<<(tree.n_nodes*8 + 127)/128, 128, 0, st>>>(scratch, tree.branch,
-                                                                   tree.n_nodes, J, D);
+  if (fold) launch_suffstats_fold(scratch, tree, J, D, st);
   return launches;
 }
 

@@ -224,6 +224,25 @@ class Context:
         self._ck(self.lib.epv_pass_end(self.h, colour, C.c_void_p(rec_lo_ptr), C.c_void_p(rec_hi_ptr)))
 
     # -- statistics -----------------------------------------------------------------
+    def stats_words(self) -> int:
+        n = C.c_uint64()
+        self._ck(self.lib.epv_stats_words(self.h, C.byref(n)))
+        return n.value
+
+    def stats_begin(self):
+        self._ck(self.lib.epv_stats_begin(self.h))
+
+    def stats_accumulate(self):
+        self._ck(self.lib.epv_stats_accumulate(self.h))
+
+    def stats_export(self, dev_ptr: int):
+        self._ck(self.lib.epv_stats_export(self.h, C.c_void_p(dev_ptr)))
+
+    def stats_fold(self, dev_ptr: Optional[int] = None):
+        J, D = np.zeros(self.n_nodes * 8), np.zeros(self.n_nodes * 8)
+        self._ck(self.lib.epv_stats_fold(self.h, C.c_void_p(dev_ptr), _d(J), _d(D)))
+        return J.reshape(-1, 8), D.reshape(-1, 8)
+
     def suffstats(self):
         J = np.zeros(self.n_nodes * 8)
         D = np.zeros(self.n_nodes * 8)
@@ -253,6 +272,16 @@ class Context:
 
     def indep_update_paths(self, rates2, seed: int, iteration: int = 0):
         self._ck(self.lib.epv_indep_update_paths(self.h, _d(_f64(rates2)), seed, iteration))
+
+    def simulate_adopt(self, n_sites: int, seed: int, root_states=None) -> int:
+        """epv_simulate + epv_simulate_adopt: the simulated histories become the context's paths
+        without leaving the device.  Returns the number of jumps."""
+        nj = C.c_uint64()
+        root = None if root_states is None else _u8(np.ascontiguousarray(root_states, np.uint8))
+        self._ck(self.lib.epv_simulate(self.h, n_sites, root, seed, C.byref(nj)))
+        self._ck(self.lib.epv_simulate_adopt(self.h))
+        self.n_sites = n_sites
+        return nj.value
 
     # -- forward simulation (epievo_sim -> global_jumps_to_paths) --------------------------
     def simulate(self, n_sites: int, seed: int, tot_time, root_states=None, node_names=()) -> PathSet:

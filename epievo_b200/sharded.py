@@ -116,6 +116,12 @@ class DistExchange:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return int(t.item())
 
+    def allreduce_int(self, t):
+        """Exact: int64 sums (the J/D accumulators and the accept count)."""
+        import torch.distributed as dist
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return t
+
     def allreduce_sum(self, arr: np.ndarray) -> np.ndarray:
         import torch
         import torch.distributed as dist
@@ -201,6 +207,32 @@ def run_mcmc(shards: Sequence[Shard], transport, burn_in: int, batch: int, seed:
     for s in shards:
         s.ctx.accept_count(reset=True)
     n_nodes = shards[0].ctx.n_nodes
+    n_global = shards[0].n_global
+    k = n_nodes * 8
+    if hasattr(shards[0].ctx, "stats_export"):
+        # exact path: the batch's J/D passes add into integer accumulators on every shard; the shards'
+        # accumulators (+ accept counts) are summed as int64 -- all-reduce across ranks -- and folded once,
+        # so J, D and the accept rate do not depend on the number of shards, to the last bit
+        import torch
+        for s in shards:
+            s.ctx.stats_begin()
+        for _ in range(batch):
+            sweep(shards, transport, seed, sw)
+            sw += 1
+            for s in shards:
+                s.ctx.stats_accumulate()
+        words = shards[0].ctx.stats_words()
+        total = None
+        for s in shards:
+            t = torch.zeros(words + 1, dtype=torch.int64, device=s.device)
+            s.ctx.stats_export(t.data_ptr())
+            t[words] = s.ctx.accept_count(reset=True)       # (synchronises the context's stream)
+            total = t if total is None else total + t.to(total.device)
+        if hasattr(transport, "allreduce_int"):
+            total = transport.allreduce_int(total)
+        torch.cuda.synchronize(total.device)
+        J, D = shards[0].ctx.stats_fold(total.data_ptr())
+        return J / batch, D / batch, float(total[words].item()) / (batch * (n_global - 2))
     Js, Ds = np.zeros((n_nodes, 8)), np.zeros((n_nodes, 8))
     for _ in range(batch):
         sweep(shards, transport, seed, sw)
@@ -213,8 +245,6 @@ def run_mcmc(shards: Sequence[Shard], transport, burn_in: int, batch: int, seed:
     flat = np.concatenate([Js.ravel(), Ds.ravel(), [acc]])
     if allreduce is not None:
         flat = allreduce(flat)
-    k = n_nodes * 8
-    n_global = shards[0].n_global
     return (flat[:k].reshape(n_nodes, 8) / batch, flat[k:2 * k].reshape(n_nodes, 8) / batch,
             flat[-1] / (batch * (n_global - 2)))
 

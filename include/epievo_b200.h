@@ -178,6 +178,20 @@ int epv_halo_set_capacity(epv_ctx *ctx, uint64_t capacity);
 int epv_set_side_stream(epv_ctx *ctx, void *cuda_stream);
 int epv_pass_begin(epv_ctx *ctx, int colour, uint64_t seed, uint64_t sweep_idx, void *rec_lo, void *rec_hi);
 int epv_pass_end(epv_ctx *ctx, int colour, const void *rec_lo, const void *rec_hi);
+/* J/D statistics as exact integer accumulators, for drivers of several shards (the fold of
+ * epv_suffstats / epv_run_mcmc is a function of integer sums only): epv_stats_begin clears the context's
+ * accumulators, epv_stats_accumulate adds one J/D pass over the current paths (enqueued only: call it
+ * after every batch sweep), epv_stats_export copies them -- epv_stats_words 8-byte words -- to a DEVICE
+ * buffer of the caller, which sums the shards' buffers element-wise as 64-bit integers (an all-reduce
+ * on int64, or peer copies + epv_stats_add), and epv_stats_fold turns a summed buffer (NULL: the
+ * context's own accumulators) into J / D [n_nodes*8] on the host.  J and D then do not depend on how the
+ * sites were sharded, to the last bit. */
+int epv_stats_words(epv_ctx *ctx, uint64_t *words);
+int epv_stats_begin(epv_ctx *ctx);
+int epv_stats_accumulate(epv_ctx *ctx);
+int epv_stats_export(epv_ctx *ctx, void *dev_words);
+int epv_stats_add(epv_ctx *ctx, const void *dev_words);
+int epv_stats_fold(epv_ctx *ctx, const void *dev_words, double *J, double *D);
 /* epv_suffstats in two halves: enqueue the pass / read the result (so that a driver of several
  * contexts has all of them running before it waits for the first). */
 int epv_suffstats_async(epv_ctx *ctx);
@@ -301,6 +315,10 @@ int epv_simulate(epv_ctx *ctx, uint64_t n_sites, const uint8_t *root_states, uin
 /* copies the result out in the epv_upload_paths exchange format: init_state [n_nodes][n_sites],
  * row_off [n_nodes*n_sites + 1] (root rows empty), jumps [n_jumps]; frees the device copy. */
 int epv_simulate_fetch(epv_ctx *ctx, uint8_t *init_state, uint64_t *row_off, double *jumps);
+/* or: the simulated histories become the context's paths without leaving the device (what
+ * epv_simulate_fetch + epv_upload_paths would load; honours epv_set_shard, n_sites of epv_simulate =
+ * the shard's local sites; refresh the halos from the neighbours afterwards). */
+int epv_simulate_adopt(epv_ctx *ctx);
 
 /* ---- local-paths text files (host only, multi-threaded) ------------- */
 /* replaces read_paths (Path.cpp:123-148): parses the file with n_threads threads

@@ -73,9 +73,10 @@ def test_multi_mcem_iteration_with_branch_updates_equals_single(model):
         finally:
             m.close()
     a, b = outs
-    assert np.allclose(a[0], b[0], rtol=1e-10) and np.allclose(a[2], b[2], rtol=1e-10)
-    assert a[3] == b[3]
-    assert a[5].same_as(b[5], rtol=1e-9)
+    # J and D are folded from integer sums over all shards: the M-step sees identical numbers
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2])
+    assert a[3] == b[3] and a[4] == b[4]
+    assert a[5].same_as(b[5])
 
 
 def test_long_branch_boundary_rows_outgrow_the_default_halo_record(model):
