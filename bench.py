@@ -100,6 +100,31 @@ class ClockSampler:
         return out
 
 
+def make_tree(workload):
+    """The workload's tree from the product's own containers (no oracle/ on the b200 arm)."""
+    from epievo_b200.paths import Tree, parse_newick
+    if workload == "bal8":
+        return Tree.balanced(8, 0.05)
+    if workload == "bal32":
+        return Tree.balanced(32, 0.05)
+    if workload == "pairwise":
+        return Tree.pair(1.0)
+    return parse_newick("((C:0.03,D:0.06)E:0.02,F:0.1)G:0.0;")     # reference test/tree.nwk
+
+
+def test_model():
+    """reference test/test.param through the library's epv_model_from_params (rates scaled)."""
+    import ctypes as C
+
+    import numpy as np
+
+    from epievo_b200 import _lib as L
+    rates, T, Q, bl = np.zeros(8), np.zeros(4), np.zeros(4), np.zeros(4)
+    d = lambda a: a.ctypes.data_as(L.dp)
+    L.load().epv_model_from_params(0.844912, 0.893359, -0.8, -1.8, 1, d(rates), d(T), d(Q), d(bl))
+    return rates, T
+
+
 def run_reference(args):
     """--impl reference: the unmodified reference CPU path on all host cores."""
     rank = int(os.environ.get("RANK", "0"))
@@ -134,12 +159,19 @@ def run_reference(args):
     return 0
 
 
-def workload_config(args, n_br, sample=None):
-    cfg = {"workload": args.workload, "description": WORKLOAD_DESC[args.workload],
-           "n_sites_per_gpu": args.sites, "n_branches": n_br, "burn_in": args.burn_in,
+def workload_config(args, n_br, sample=None, n_global=None, world=1, gen="host"):
+    desc = WORKLOAD_DESC[args.workload]
+    if args.sites != DEFAULT_SITES[args.workload] or args.scaling == "strong":
+        desc += " [run at --sites %d, %s scaling]" % (args.sites, args.scaling)
+    per_gpu = args.sites if args.scaling == "weak" else (n_global or args.sites) // max(1, world)
+    cfg = {"workload": args.workload, "description": desc,
+           "n_sites_per_gpu": per_gpu, "n_sites_total": n_global or args.sites, "n_branches": n_br,
+           "histories": "numpy generator + upload" if gen == "host" else "epv_simulate on the device, adopted in place",
+           "burn_in": args.burn_in,
            "batch": args.batch, "step": "one run_mcmc E-step = (L+B) sweeps + B J/D passes",
            "parallelism": "contiguous site blocks, one per GPU; 3-site halos, one NCCL send/recv pair "
-                          "per neighbour per colour pass, one all-reduce of J/D per E-step",
+                          "per neighbour per colour pass (edge groups first on a side stream, the exchange "
+                          "overlaps the interior update), one int64 all-reduce of the J/D accumulators per E-step",
            "l2": "inputs (>=0.5 GB of rows per pass) are larger than the 126 MB L2"}
     if sample:
         cfg["sample"] = sample
@@ -162,6 +194,17 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-mcem", action="store_true")
+    ap.add_argument("--scaling", choices=("weak", "strong"), default="weak",
+                    help="weak: --sites per GPU; strong: --sites in total, split over the GPUs")
+    ap.add_argument("--gen", choices=("auto", "host", "device"), default="auto",
+                    help="synthetic histories from the numpy generator (host) or epv_simulate on the GPU "
+                         "(device: shards too large to stage through host arrays; no e2e leg); "
+                         "auto = device above 4e8 rows per GPU")
+    ap.add_argument("--optimize-branches", action="store_true",
+                    help="the MCEM iteration updates branch lengths too (the reference's -b)")
+    ap.add_argument("--serial-exchange", action="store_true",
+                    help="N>1: the round-1 protocol (pass, pack, exchange, unpack on one stream) "
+                         "instead of the overlapped one")
     ap.add_argument("--exchange", choices=("compact", "csr"), default="compact",
                     help="host exchange format of the e2e leg (u16 row codes, or 9-byte CSR rows)")
     args = ap.parse_args()
@@ -174,8 +217,6 @@ def main():
     import torch
     import torch.distributed as dist
 
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
-    import cpu_bench                      # make_tree / test_model helpers + the CPU leg
     from epievo_b200.device import Context
     from epievo_b200.synthetic import simulate_paths
 
@@ -194,37 +235,18 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    tree = cpu_bench.make_tree(args.workload)
-    rates, T = cpu_bench.test_model()
+    tree = make_tree(args.workload)
+    rates, T = test_model()
     n_br = tree.n_nodes - 1
     sweeps = args.burn_in + args.batch
     from epievo_b200 import sharded as S
     from epievo_b200.paths import PathSet
-    n_global = args.sites * world
+    n_global = args.sites * world if args.scaling == "weak" else args.sites
     lo, hi, halo_lo, halo_hi = S.shard_bounds(n_global, world, rank)
     n_own = hi - lo
-    ps = simulate_paths(tree, n_own, rates, T, seed=12345 + rank)
-    if world > 1:
-        # neighbours' boundary sites become this rank's halos (gathered once, at setup)
-        edges = [None] * world
-        dist.all_gather_object(edges, (ps.site_slice(0, S.HALO), ps.site_slice(n_own - S.HALO, n_own)))
-        parts = ([edges[rank - 1][1]] if halo_lo else []) + [ps] + ([edges[rank + 1][0]] if halo_hi else [])
-        ps = PathSet.concat_sites(parts)
-    n = ps.n_sites                          # local sites: owned block + halos
-
-    # pinned host buffers in the C-ABI exchange format (jumps sized with headroom)
+    n = n_own + halo_lo + halo_hi           # local sites: owned block + halos
     n_rows = n * tree.n_nodes
-    jcap = int(ps.jumps.size * 1.5) + 65536
-    h_init = torch.empty(n_rows, dtype=torch.uint8, pin_memory=True)
-    h_off = torch.empty(n_rows + 1, dtype=torch.int64, pin_memory=True)
-    h_jmp = torch.empty(jcap, dtype=torch.float64, pin_memory=True)
-    h_init.numpy()[:] = ps.init_state
-    h_off.numpy()[:] = ps.row_off.view(np.int64)
-    h_jmp.numpy()[:ps.jumps.size] = ps.jumps
-    h_code = torch.empty(n_rows, dtype=torch.int16, pin_memory=True)   # compact format: u16 codes
-    nj_host = int(ps.jumps.size)
-    tot_time = ps.tot_time.copy()
-    del ps
+    gen = args.gen if args.gen != "auto" else ("device" if n_rows > 4e8 else "host")
 
     ctx = Context(local)
     stream = torch.cuda.Stream()           # a real (non-default) stream the context launches on
@@ -236,7 +258,39 @@ def main():
     if world > 1:
         shard = S.Shard(ctx, n_global, world, rank, torch.device("cuda", local))
         transport = S.DistExchange(shard)
-    ctx.upload_raw(n, tree.n_nodes, h_init.data_ptr(), h_off.data_ptr(), h_jmp.data_ptr(), tot_time)
+    tot_time = np.array(tree.branches, np.float64)
+    tot_time[0] = 0.0
+    h_init = h_off = h_jmp = h_code = None
+    jcap = nj_host = 0
+    if gen == "host":
+        ps = simulate_paths(tree, n_own, rates, T, seed=12345 + rank)
+        if world > 1:
+            # neighbours' boundary sites become this rank's halos (gathered once, at setup)
+            edges = [None] * world
+            dist.all_gather_object(edges, (ps.site_slice(0, S.HALO), ps.site_slice(n_own - S.HALO, n_own)))
+            parts = ([edges[rank - 1][1]] if halo_lo else []) + [ps] + ([edges[rank + 1][0]] if halo_hi else [])
+            ps = PathSet.concat_sites(parts)
+        assert ps.n_sites == n
+        # pinned host buffers in the C-ABI exchange format (jumps sized with headroom)
+        jcap = int(ps.jumps.size * 1.5) + 65536
+        h_init = torch.empty(n_rows, dtype=torch.uint8, pin_memory=True)
+        h_off = torch.empty(n_rows + 1, dtype=torch.int64, pin_memory=True)
+        h_jmp = torch.empty(jcap, dtype=torch.float64, pin_memory=True)
+        h_init.numpy()[:] = ps.init_state
+        h_off.numpy()[:] = ps.row_off.view(np.int64)
+        h_jmp.numpy()[:ps.jumps.size] = ps.jumps
+        h_code = torch.empty(n_rows, dtype=torch.int16, pin_memory=True)   # compact format: u16 codes
+        nj_host = int(ps.jumps.size)
+        tot_time = ps.tot_time.copy()
+        del ps
+        ctx.upload_raw(n, tree.n_nodes, h_init.data_ptr(), h_off.data_ptr(), h_jmp.data_ptr(), tot_time)
+    else:
+        # shards too large to stage through host arrays (config 5: 7.9e8 rows per GPU): the library's own
+        # forward simulator writes the histories on the device and the context adopts them; every rank
+        # simulates its local sites and then takes its halo rows from the neighbours
+        ctx.simulate_adopt(n, 12345 + rank)
+        if world > 1:
+            S.refresh_halos([shard], transport)
     ctx.reset()
 
     def e_step(first_sweep):
@@ -245,7 +299,8 @@ def main():
         if world == 1:
             return ctx.run_mcmc(args.burn_in, args.batch, seed=2024, first_sweep=first_sweep)
         return S.run_mcmc([shard], transport, args.burn_in, args.batch, seed=2024,
-                          first_sweep=first_sweep, allreduce=transport.allreduce_sum)
+                          first_sweep=first_sweep, allreduce=transport.allreduce_sum,
+                          overlap=not args.serial_exchange)
 
     sweep_no = 0
     for _ in range(args.warmup):
@@ -285,7 +340,7 @@ def main():
 
     # ---- timed region 2: end to end through the C-ABI with host buffers --------------
     e2e = None
-    if not args.no_e2e:
+    if not args.no_e2e and gen == "host":
         n_sites_, n_nodes_, nj = ctx.paths_size()
         if nj > jcap:
             raise SystemExit("bench.py: pinned jump buffer too small")
@@ -372,9 +427,11 @@ def main():
     # between device synchronisations (the M-step runs on the host), max over ranks.
     def mcem_once(first_sweep):
         if world == 1:
-            return ctx.mcem_iteration(args.burn_in, args.batch, 2024, first_sweep, rates, T, tree.branches)
+            return ctx.mcem_iteration(args.burn_in, args.batch, 2024, first_sweep, rates, T, tree.branches,
+                                      optimize_branches=args.optimize_branches)
         return S.mcem_iteration([shard], transport, args.burn_in, args.batch, 2024, first_sweep, rates, T,
-                                tree.branches, allreduce=transport.allreduce_sum)
+                                tree.branches, optimize_branches=args.optimize_branches,
+                                allreduce=transport.allreduce_sum, overlap=not args.serial_exchange)
     mcem = None
     if not args.no_mcem:
         barrier()
@@ -387,7 +444,8 @@ def main():
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         sweep_no += sweeps
         mcem = {"ms": float(dt.item()) * 1e3, "burn_in": args.burn_in, "batch": args.batch,
-                "sites": int(n_global), "acc_rate": float(out[4]),
+                "sites": int(n_global), "acc_rate": float(out[4]), "optimize_branches": bool(args.optimize_branches),
+                "peak_device_memory_gb": (torch.cuda.mem_get_info()[1] - torch.cuda.mem_get_info()[0]) / 1e9,
                 "what": "set_model + reset + run_mcmc(L,B) + M-step (estimate_rates, host) + scale_jump_times"}
 
     # ---- CPU baseline (rank 0, N=1 only) ---------------------------------------------------
@@ -395,6 +453,8 @@ def main():
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         n_s = 50_000
         bi, ba = 5, 5
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import cpu_bench                  # the CPU leg only: the checker timed, never part of the GPU arm
         kind, per_step = cpu_bench.run(args.workload, n_s, bi, ba, 1, 1)
         cpu_baseline = {"value": (n_s - 2) * n_br * (bi + ba) / per_step[0], "unit": UNIT, "cores": 1,
                         "kind": kind,
@@ -408,8 +468,8 @@ def main():
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": workload_config(args, n_br), "clocks": clk, "e2e": e2e,
+            "scaling": args.scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(args, n_br, n_global=n_global, world=world, gen=gen), "clocks": clk, "e2e": e2e,
             "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu_baseline,
             "acc_rate": acc, "suffstats_pass": suffstats, "mcem_iter": mcem,
         }

@@ -82,7 +82,7 @@ int one_pass(epv_ctx *c, int colour, uint64_t seed, uint32_t sweep, const IndepL
   a.err = c->d_err; a.n_accept = c->d_nacc;
   a.n_groups = c->n_groups; a.stage_off = c->d_stg_off; a.stage = c->d_stg;
   a.stage_ctr = c->d_stg_ctr; a.stage_cap = c->stg_cap;
-  a.ovf_list = c->d_ovf_list; a.list_mode = 0;
+  a.ovf_list = c->d_ovf_list; a.list_mode = 0; a.reverse = 0;
   EPV_CUDA(c, cudaMemsetAsync(c->d_ovf_list, 0, sizeof(uint32_t), c->stream));
   EPV_CUDA(c, cudaMemsetAsync(c->d_scratch_ctr, 0, sizeof(uint32_t), c->stream));
   EPV_CUDA(c, cudaMemsetAsync(c->d_stg_ctr, 0, sizeof(unsigned long long), c->stream));

@@ -42,6 +42,7 @@ struct PassArgs {
   uint64_t n_groups;          // groups of 3 sites covering the local sites
   // groups one launch works on: index i < g_count maps to group g_first + i (+ g_skip when i >= g_split)
   uint64_t g_first, g_split, g_skip, g_count;
+  int reverse;                // test-only (EPIEVO_B200_REVERSE): thread i takes group g_count-1-i -- another schedule, same chain
   uint32_t *ovf_list;         // [1 + n_groups]: count, then the groups the main update launch deferred
   int list_mode;              // the launch works on ovf_list instead of a group range
   uint32_t *stage_off;        // [n_groups] offset into stage, or rejected / empty marker

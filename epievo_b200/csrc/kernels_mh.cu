@@ -56,8 +56,15 @@ __host__ __device__ constexpr int mh_minblocks(int maxn) { return maxn <= 16 ? 4
 // active lanes) instead of once per site.  Kept behind EPV_MH_LOCK as the base of the next step.
 // EPV_MH_IMPL: 0 = mh_site_flat, 1 = mh_site_lock, 2 = mh_site_mix (mh_mix.cuh: lockstep for the
 // single-interval branches, per-lane flat loops for the others); trees wider than 64 nodes always 0.
+// Measured on the B200 (ms per colour pass, flat / lock / mix): 8-leaf tree 5.12 / 6.56 / 8.27, test tree
+// 5.64 / 7.30 / 8.33, 32-leaf tree 7.52 / 8.48 / 19.2 (its shared arrays leave 2 CTAs per SM), 1e6-site
+// single branch 0.41 / 0.44 / 0.53: the flat routine stays the default; all three pass the exact-posterior
+// tests (tests/test_gpu_exact_posterior.py).
 #ifndef EPV_MH_IMPL
-#define EPV_MH_IMPL 2
+#define EPV_MH_IMPL 0
+#endif
+#ifndef EPV_MH_QSMEM            // lock / mix: Felsenstein q of the internal nodes in shared memory (else local)
+#define EPV_MH_QSMEM 1
 #endif
 __host__ __device__ constexpr int mh_impl(int maxn) { return maxn <= 64 ? EPV_MH_IMPL : 0; }
 __host__ __device__ constexpr bool mh_lock(int maxn) { return mh_impl(maxn) != 0; }
@@ -262,7 +269,8 @@ mh_update_kernel(const PassArgs a, int q_slots) {
     __syncthreads();
   }
   if (!HALO) {
-    const uint64_t gi = (uint64_t)blockIdx.x*MH_THREADS + t;
+    uint64_t gi = (uint64_t)blockIdx.x*MH_THREADS + t;
+    if (a.reverse && gi < a.g_count) gi = a.g_count - 1 - gi;
     const uint64_t g = gi >= a.g_count ? a.n_groups                // group of sites 3g..3g+2
                                        : a.g_first + gi + (gi >= a.g_split ? a.g_skip : 0);
     mh_update_group<MAXN, MAXJ, false, DEFER, QSMEM>(a, s_mp, s_tb, sh, g);
@@ -474,7 +482,7 @@ template <int MAXN, int MAXJ, bool HALO, bool DEFER>
 static void
 launch_variant(const PassArgs &a, unsigned blocks, cudaStream_t st) {
   size_t off[7];
-  const bool qsmem = mh_lock(MAXN) && mh_smem_layout<MAXN>(a.tree.n_nodes, a.q_slots, off) <= smem_budget<MAXN>();
+  const bool qsmem = EPV_MH_QSMEM && mh_lock(MAXN) && mh_smem_layout<MAXN>(a.tree.n_nodes, a.q_slots, off) <= smem_budget<MAXN>();
   if (qsmem) {
     const size_t smem = mh_smem_layout<MAXN>(a.tree.n_nodes, a.q_slots, off);
     cudaFuncSetAttribute(mh_update_kernel<MAXN, MAXJ, HALO, DEFER, mh_lock(MAXN)>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -492,6 +500,7 @@ static int
 launch_interior_t(const PassArgs &a0, cudaStream_t st) {
   PassArgs a = a0;
   a.list_mode = 0;
+  a.reverse = getenv("EPIEVO_B200_REVERSE") != nullptr;
   uint64_t g_lo, g_hi; edge_split(a, g_lo, g_hi);
   if (g_hi <= g_lo) return 0;
   // deferral costs one more launch whose length is the latency of a single site update (~0.1 ms

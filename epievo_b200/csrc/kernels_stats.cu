@@ -46,10 +46,10 @@ struct StatsAcc {
 __device__ __forceinline__ void
 flush_acc(const StatsAcc &A, int i, unsigned long long *acc) {
   const int bi = i >> 3, t = i & 7;
-  const unsigned long long d = (unsigned long long)A.Dfix[i];
+  const long long d = A.Dfix[i];                 // signed: an event's time is added to one bin, taken from another
   if (d) {
-    atomicAdd(acc + bi*SS_ACC + t, d & 0xffffffffull);
-    atomicAdd(acc + bi*SS_ACC + 24 + t, d >> 32);
+    atomicAdd(acc + bi*SS_ACC + t, (unsigned long long)d & 0xffffffffull);
+    atomicAdd(acc + bi*SS_ACC + 24 + t, (unsigned long long)(d >> 32));
   }
   if (A.J[i]) atomicAdd(acc + bi*SS_ACC + 8 + t, (unsigned long long)A.J[i]);
   if (A.C[i]) atomicAdd(acc + bi*SS_ACC + 16 + t, (unsigned long long)A.C[i]);
@@ -74,11 +74,14 @@ load3(const PathView &pv, const uint8_t *state, int W, int bi, uint64_t s, Row &
   }
 }
 
-// Three-way merge of one row triple (add_sufficient_statistics, Path.cpp:267-301).
+// Three-way merge of one row triple (add_sufficient_statistics, Path.cpp:267-301).  D is accumulated
+// through the same identity and the SAME integers as the tile kernel below -- an event at time t adds
+// fix(t) to the bin of the triplet before it and takes it from the bin of the triplet after it, the final
+// triplet goes to the row counter C (the fold multiplies it by the branch length) -- so the integer sums,
+// hence J and D, do not depend on which kernel a row went to (i.e. on where the shard ends are).
 __device__ __forceinline__ void
 merge_row(const Row &L, const Row &M, const Row &R, double tot, const StatsAcc &A, int bi) {
   int trip = L.init*4 + M.init*2 + R.init, i = 0, j = 0, k = 0;
-  double prev = 0.0;
   const double scale = SS_FIX/tot;
   const double INF = __longlong_as_double(0x7ff0000000000000LL);
   for (;;) {
@@ -89,13 +92,12 @@ merge_row(const Row &L, const Row &M, const Row &R, double tot, const StatsAcc &
     if (tl < fmin(tm, tr)) { tn = tl; flip = 4; ++i; }
     else if (tm < tr) { tn = tm; flip = 2; ++j; }
     else { tn = tr; flip = 1; ++k; }
-    const bool end = !(tn < INF);
-    if (end) tn = tot;
-    atomicAdd(reinterpret_cast<unsigned long long *>(&A.Dfix[bi*8 + trip]),
-              (unsigned long long)__double2ll_rn((tn - prev)*scale));
-    if (end) break;
+    if (!(tn < INF)) { atomicAdd(&A.C[bi*8 + trip], 1u); break; }
+    const unsigned long long f = (unsigned long long)__double2ll_rn(tn*scale);
+    atomicAdd(reinterpret_cast<unsigned long long *>(&A.Dfix[bi*8 + trip]), f);
+    atomicAdd(reinterpret_cast<unsigned long long *>(&A.Dfix[bi*8 + (trip ^ flip)]), 0ull - f);
     if (flip == 2) atomicAdd(&A.J[bi*8 + trip], 1u);
-    prev = tn; trip ^= flip;
+    trip ^= flip;
   }
 }
 

@@ -5,6 +5,8 @@
 #include "SingleSiteSampler.hpp"
 
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
 #include <cstdlib>
 #include <stdexcept>
 #include <string>
@@ -19,6 +21,22 @@ int_from_env(const char *name, int dflt) {
   const char *e = std::getenv(name);
   return e && *e ? std::atoi(e) : dflt;
 }
+
+/* EPIEVO_B200_TIMING=1: seconds spent per phase of the drop-in calls, printed to stderr when the sampler
+ * is destroyed (tools/cli_bench.py reads it). */
+namespace {
+struct PhaseClock {
+  double flatten = 0, upload = 0, device = 0, download = 0, unflatten = 0;
+  size_t calls = 0;
+  const bool on = std::getenv("EPIEVO_B200_TIMING") != nullptr;
+  ~PhaseClock() {
+    if (on && calls)
+      std::fprintf(stderr, "[epievo_b200 timing] calls=%zu flatten=%.4f upload=%.4f device=%.4f download=%.4f unflatten=%.4f\n",
+                   calls, flatten, upload, device, download, unflatten);
+  }
+} phase_clock;
+double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+}  // namespace
 
 static epv_multi *
 new_context() {
@@ -77,6 +95,7 @@ for_site_ranges(size_t n_sites, size_t n_threads, F f) {
 void
 SingleSiteSampler::upload(const vector<vector<Path> > &paths, const TreeHelper &th) {
   const size_t n_sites = paths.size(), n_nodes = th.n_nodes;
+  const double t0 = now_s();
   init_state.assign(n_sites*n_nodes, 0);
   row_off.assign(n_sites*n_nodes + 1, 0);
   tot_time.assign(n_nodes, 0.0);
@@ -104,18 +123,23 @@ SingleSiteSampler::upload(const vector<vector<Path> > &paths, const TreeHelper &
     }
   });
   row_off[n_sites*n_nodes] = total;
+  const double t1 = now_s();
   check(epv_multi_upload_paths(ctx, n_sites, n_nodes, init_state.data(),
                                reinterpret_cast<const uint64_t *>(row_off.data()), jumps.data(),
                                tot_time.data()));
+  phase_clock.flatten += t1 - t0; phase_clock.upload += now_s() - t1; ++phase_clock.calls;
 }
 
 void
 SingleSiteSampler::download(vector<vector<Path> > &paths) {
   uint64_t n_sites = 0, n_nodes = 0, n_jumps = 0;
+  const double t0 = now_s();
   check(epv_multi_paths_size(ctx, &n_sites, &n_nodes, &n_jumps));
   jumps.resize(n_jumps ? n_jumps : 1);
   check(epv_multi_download_paths(ctx, init_state.data(), reinterpret_cast<uint64_t *>(row_off.data()),
                                  jumps.data(), tot_time.data()));
+  const double t1 = now_s();
+  phase_clock.download += t1 - t0;
   for_site_ranges(n_sites, host_threads(n_sites*n_nodes), [&](size_t, size_t s0, size_t s1) {
     for (size_t s = s0; s < s1; ++s)
       for (size_t b = 1; b < n_nodes; ++b) {
@@ -126,6 +150,7 @@ SingleSiteSampler::download(vector<vector<Path> > &paths) {
         p.jumps.assign(jumps.begin() + row_off[r], jumps.begin() + row_off[r + 1]);
       }
   });
+  phase_clock.unflatten += now_s() - t1;
 }
 
 /* The reference caches tri_llh here (SingleSiteSampler.cpp:449-475).  The device cache
@@ -148,7 +173,9 @@ SingleSiteSampler::Metropolis_Hastings_site(const EpiEvoModel &the_model, const 
   configure(the_model, th);
   upload(paths, th);
   uint64_t n_acc = 0;
+  const double t0 = now_s();
   check(epv_multi_sweep(ctx, seed_from(gen), sweep_counter++, &n_acc));
+  phase_clock.device += now_s() - t0;
   download(paths);
   last_sweep_accepts = n_acc;
   return n_acc > 0;
@@ -162,8 +189,10 @@ SingleSiteSampler::run_mcmc(const EpiEvoModel &the_model, const TreeHelper &th,
   configure(the_model, th);
   upload(paths, th);
   vector<double> J(th.n_nodes*8), D(th.n_nodes*8);
+  const double t0 = now_s();
   check(epv_multi_run_mcmc(ctx, burn_in, batch, seed_from(gen), sweep_counter, J.data(), D.data(),
                            &acceptance_rate));
+  phase_clock.device += now_s() - t0;
   sweep_counter += burn_in + batch;
   download(paths);
   J_all_sites.assign(th.n_nodes, vector<double>(8, 0.0));   // row 0 unused, as the reference

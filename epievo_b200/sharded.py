@@ -169,10 +169,34 @@ def colour_pass(shards: Sequence[Shard], transport, colour: int, seed: int, swee
         return
     for s in shards:
         s.ctx.colour_pass(colour, seed, sweep)
+    _serial_exchange(shards, transport, colour)
+
+
+def _serial_exchange(shards: Sequence[Shard], transport, colour: int):
+    """pack (main streams) -> records move (side streams) -> unpack (main streams), with host
+    synchronisations in between: the round-1 protocol, kept for comparison and for set-up."""
+    for s in shards:
         s.pack(colour)
+    for s in shards:
+        if s.side is not None:
+            s.ctx.synchronize()
     transport.exchange()
     for s in shards:
+        if s.side is not None:
+            s.side.synchronize()
+    for s in shards:
         s.unpack(colour)
+
+
+def refresh_halos(shards: Sequence[Shard], transport):
+    """Every shard's halo rows := its neighbours' boundary sites (after histories were created shard by
+    shard, e.g. epv_simulate_adopt): the three boundary sites of either side travel as the records of
+    colours 0, 1, 2.  The tri_llh cache is not valid afterwards (call reset)."""
+    agree_halo_capacity(shards, transport, grow=False)
+    for colour in range(3):
+        _serial_exchange(shards, transport, colour)
+    # boundary rows longer than half a record: grow before the first sweep
+    agree_halo_capacity(shards, transport, grow=True)
 
 
 def agree_halo_capacity(shards: Sequence[Shard], transport, grow: bool = True):
@@ -196,13 +220,13 @@ def sweep(shards: Sequence[Shard], transport, seed: int, sweep_idx: int, overlap
 
 
 def run_mcmc(shards: Sequence[Shard], transport, burn_in: int, batch: int, seed: int,
-             first_sweep: int = 0, allreduce=None):
+             first_sweep: int = 0, allreduce=None, overlap: bool = True):
     """SingleSiteSampler::run_mcmc (reference SingleSiteSampler.cpp:550-598) over shards.
     Returns batch-averaged J, D [n_nodes, 8] and the acceptance rate over all sites."""
     sw = first_sweep
     agree_halo_capacity(shards, transport, grow=False)     # uploads size it per shard
     for _ in range(burn_in):
-        sweep(shards, transport, seed, sw)
+        sweep(shards, transport, seed, sw, overlap)
         sw += 1
     for s in shards:
         s.ctx.accept_count(reset=True)
@@ -217,7 +241,7 @@ def run_mcmc(shards: Sequence[Shard], transport, burn_in: int, batch: int, seed:
         for s in shards:
             s.ctx.stats_begin()
         for _ in range(batch):
-            sweep(shards, transport, seed, sw)
+            sweep(shards, transport, seed, sw, overlap)
             sw += 1
             for s in shards:
                 s.ctx.stats_accumulate()
@@ -235,7 +259,7 @@ def run_mcmc(shards: Sequence[Shard], transport, burn_in: int, batch: int, seed:
         return J / batch, D / batch, float(total[words].item()) / (batch * (n_global - 2))
     Js, Ds = np.zeros((n_nodes, 8)), np.zeros((n_nodes, 8))
     for _ in range(batch):
-        sweep(shards, transport, seed, sw)
+        sweep(shards, transport, seed, sw, overlap)
         sw += 1
         for s in shards:
             J, D = s.ctx.suffstats()
@@ -251,7 +275,7 @@ def run_mcmc(shards: Sequence[Shard], transport, burn_in: int, batch: int, seed:
 
 def mcem_iteration(shards: Sequence[Shard], transport, burn_in: int, batch: int, seed: int,
                    first_sweep: int, rates, T, branches, optimize_branches: bool = False,
-                   param_tol: float = 1e-10, allreduce=None):
+                   param_tol: float = 1e-10, allreduce=None, overlap: bool = True):
     """One MCEM iteration over shards -- the body of the loop at
     prog/epievo_est_params_histories.cpp:239-264, i.e. what epv_mcem_iteration does on one
     GPU: new model -> reset -> E-step (run_mcmc, J/D all-reduced) -> M-step on the host
@@ -268,7 +292,7 @@ def mcem_iteration(shards: Sequence[Shard], transport, burn_in: int, batch: int,
     for s in shards:
         s.ctx.set_model(r, t)
         s.ctx.reset()
-    J, D, acc = run_mcmc(shards, transport, burn_in, batch, seed, first_sweep, allreduce=allreduce)
+    J, D, acc = run_mcmc(shards, transport, burn_in, batch, seed, first_sweep, allreduce=allreduce, overlap=overlap)
     Jf, Df = np.ascontiguousarray(J.reshape(-1)), np.ascontiguousarray(D.reshape(-1))
     n_nodes = shards[0].ctx.n_nodes
 

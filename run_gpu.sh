@@ -1,12 +1,15 @@
-# GPU-box session (round 2, session 4): mix update kernel (default) vs flat; multi-GPU handle with exact J/D
+# GPU-box session (round 2, session 5): no-alloc entry point, exact J/D over shards, -b over seeds, colour sets,
+# drop-in CLI timing; A/B + profile of the mix update routine (default is the flat routine again)
 mkdir -p gpurun_out
-FLAT=$PWD/epievo_b200/variants/libepievo_flat.so
-EPIEVO_B200_LIB=$FLAT timeout 600 python -m pytest tests/test_gpu_chain_golden.py tests/test_gpu_multi.py tests/test_gpu_sharded.py -m gpu -x -q > gpurun_out/r02_pytest_s4_flat.log 2>&1; echo "pytest rc=$?" >> gpurun_out/r02_pytest_s4_flat.log
-tail -6 gpurun_out/r02_pytest_s4_flat.log
-timeout 1500 python -m pytest tests -m gpu -q --deselect tests/test_gpu_chain_golden.py > gpurun_out/r02_pytest_s4_mix.log 2>&1; echo "pytest rc=$?" >> gpurun_out/r02_pytest_s4_mix.log
-tail -30 gpurun_out/r02_pytest_s4_mix.log
-for w in bal8 testtree bal32 pairwise; do
-  timeout 300 python bench.py --workload $w --no-cpu-baseline --no-mcem --no-e2e > gpurun_out/bench_s4_$w.json 2> gpurun_out/bench_s4_$w.err; tail -c 700 gpurun_out/bench_s4_$w.json | head -c 400; echo
+timeout 300 python -m pytest tests/test_zz_no_alloc.py -m gpu -q > gpurun_out/r02_pytest_noalloc_alone.log 2>&1; echo "pytest rc=$?" >> gpurun_out/r02_pytest_noalloc_alone.log
+tail -4 gpurun_out/r02_pytest_noalloc_alone.log
+timeout 1200 python -m pytest tests/test_gpu_multi.py tests/test_gpu_mcem.py tests/test_gpu_colour_sets.py tests/test_gpu_chain_golden.py tests/test_gpu_sharded.py tests/test_gpu_parity.py tests/test_gpu_compact.py tests/test_gpu_dropin_cli.py tests/test_zz_no_alloc.py -m gpu -q > gpurun_out/r02_pytest_s5.log 2>&1; echo "pytest rc=$?" >> gpurun_out/r02_pytest_s5.log
+tail -25 gpurun_out/r02_pytest_s5.log
+timeout 900 python tools/cli_bench.py > gpurun_out/r02_cli_bench.json 2> gpurun_out/r02_cli_bench.err; tail -5 gpurun_out/r02_cli_bench.err; head -c 1500 gpurun_out/r02_cli_bench.json
+for v in mix mixlocal; do
+  EPIEVO_B200_LIB=$PWD/epievo_b200/variants/libepievo_$v.so timeout 300 python bench.py --workload bal8 --no-cpu-baseline --no-mcem --no-e2e > gpurun_out/bench_s5_${v}_bal8.json 2> gpurun_out/bench_s5_${v}_bal8.err
+  python -c "import json; d=json.load(open('gpurun_out/bench_s5_${v}_bal8.json')); print('$v', d['roofline']['avg_launch_ms'])"
 done
-timeout 900 python tools/stats_probe.py --arm gpu --R 2048 --burn 300 > gpurun_out/r02_stats_probe_mix_bal8_R2048_burn300.txt 2>&1
-tail -6 gpurun_out/r02_stats_probe_mix_bal8_R2048_burn300.txt
+B="python bench.py --steps 1 --warmup 1 --burn-in 1 --batch 1 --no-e2e --no-cpu-baseline --no-mcem"
+EPIEVO_B200_LIB=$PWD/epievo_b200/variants/libepievo_mix.so timeout 600 ncu --set full --clock-control none --import-source on -k regex:"mh_update" -s 6 -c 2 -o gpurun_out/prof_mix $B > gpurun_out/ncu_mix.log 2>&1
+tail -2 gpurun_out/ncu_mix.log

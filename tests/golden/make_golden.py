@@ -71,6 +71,27 @@ def make_cli():
     os.remove(out + "/mcem_b.paths")
 
 
+def make_cli_b_seeds():
+    """-b (branch lengths optimised too): final parameters AND branch lengths of the CPU reference binary
+    over 12 seeds, `-b -i 3 -B 10 -L 10` on the walk-through data (for tests/test_gpu_mcem.py)."""
+    from epievo_b200.paths import read_tree
+    out = os.path.join(HERE, "cli")
+    tree, param = os.path.join(out, "tree.nwk"), os.path.join(out, "test.param")
+    rows = []
+    for seed in range(1, 13):
+        sh([BIN + "/epievo_est_params_histories", "-b", "-s", str(seed), "-i", "3", "-B", "10", "-L", "10",
+            "-o", out + "/_tmp.paths", "-p", out + "/_tmp.param", "-t", out + "/_tmp.nwk", param, tree,
+            out + "/sim.paths"])
+        vals = [l.split()[1:] for l in open(out + "/_tmp.param")]
+        br = read_tree(out + "/_tmp.nwk").branches[1:]
+        rows.append("%d\t%s\t%s\t%s\t%s\t%s\n" % (seed, vals[0][0], vals[0][1], vals[1][0], vals[1][1],
+                                                   "\t".join(repr(float(b)) for b in br)))
+    open(out + "/mcem_b_seeds.tsv", "w").write("seed\tT00\tT11\tbaseline00\tbaseline11\tbranch1\tbranch2\tbranch3\tbranch4\n"
+                                               + "".join(rows))
+    for f in ("_tmp.paths", "_tmp.param", "_tmp.nwk"):
+        os.remove(os.path.join(out, f))
+
+
 def make_init():
     """epievo_initialization (site-independent EM + resampled starting paths) by the reference
     binary: the deterministic EM trajectory of -s 1, and the final parameters over 12 seeds."""
@@ -143,8 +164,11 @@ if __name__ == "__main__":
     assert cpu_libs.ref_available(), "build oracle/_ref first: make -C oracle ref"
     if "--init-only" in sys.argv:        # adds the epievo_initialization fixtures, keeps the rest
         make_init()
+    elif "--b-seeds-only" in sys.argv:   # adds the -b trajectories over seeds, keeps the rest
+        make_cli_b_seeds()
     else:
         make_cli()
+        make_cli_b_seeds()
         make_init()
         make_lib()
     print("golden vectors written to", HERE)
