@@ -62,6 +62,8 @@ SIGNATURES = {
     "epv_stats_export": (C.c_int, [ctx_p, C.c_void_p]),
     "epv_stats_add": (C.c_int, [ctx_p, C.c_void_p]),
     "epv_stats_fold": (C.c_int, [ctx_p, C.c_void_p, dp, dp]),
+    "epv_suffstats_static": (C.c_int, [ctx_p, dp, dp]),
+    "epv_static_limits": (C.c_int, [u64p, u64p]),
     "epv_suffstats_async": (C.c_int, [ctx_p]),
     "epv_suffstats_fetch": (C.c_int, [ctx_p, dp, dp]),
     "epv_multi_create": (C.c_int, [C.POINTER(ctx_p), C.c_int, C.POINTER(C.c_int)]),

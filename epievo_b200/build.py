@@ -14,7 +14,7 @@ LIB = os.path.join(HERE, "libepievo_b200.so")
 OBJ = os.path.join(HERE, "build")
 
 CU_SOURCES = ["kernels_mh.cu", "kernels_aux.cu", "kernels_stats.cu", "kernels_halo.cu", "kernels_compact.cu", "kernels_indep.cu",
-              "api_core.cu", "api_paths.cu", "api_sampler.cu", "api_debug.cu", "api_halo.cu", "api_sim.cu", "api_multi.cu"]
+              "api_core.cu", "api_paths.cu", "api_sampler.cu", "api_debug.cu", "api_halo.cu", "api_sim.cu", "api_multi.cu", "api_noalloc.cu"]
 CXX_SOURCES = ["host_model.cpp", "paths_io.cpp"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fno-fast-math", "--fmad=true"]

@@ -243,6 +243,14 @@ class Context:
         self._ck(self.lib.epv_stats_fold(self.h, C.c_void_p(dev_ptr), _d(J), _d(D)))
         return J.reshape(-1, 8), D.reshape(-1, 8)
 
+    def suffstats_static(self):
+        """epv_suffstats_static: the J/D pass with its scratch in the library's static device array
+        (no allocation; trees of at most 64 nodes)."""
+        J = np.zeros(self.n_nodes * 8)
+        D = np.zeros(self.n_nodes * 8)
+        self._ck(self.lib.epv_suffstats_static(self.h, _d(J), _d(D)))
+        return J.reshape(-1, 8), D.reshape(-1, 8)
+
     def suffstats(self):
         J = np.zeros(self.n_nodes * 8)
         D = np.zeros(self.n_nodes * 8)

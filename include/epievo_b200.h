@@ -192,6 +192,18 @@ int epv_stats_accumulate(epv_ctx *ctx);
 int epv_stats_export(epv_ctx *ctx, void *dev_words);
 int epv_stats_add(epv_ctx *ctx, const void *dev_words);
 int epv_stats_fold(epv_ctx *ctx, const void *dev_words, double *J, double *D);
+/* epv_suffstats WITHOUT any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same kernels and same result as epv_suffstats on the context's resident
+ * paths (J exact, D bit-identical: integer accumulation); the scratch the kernels accumulate into is a
+ * file-scope device array of the library (csrc/api_noalloc.cu) instead of the context's buffer.
+ * LIMIT: trees of at most 64 nodes (the array is 40 320 bytes; every GPU that loads the library holds it
+ * until the process exits; epv_static_limits reports both numbers).  A larger tree is rejected with an
+ * error, nothing is launched.  The call itself calls no cudaMalloc / cudaFree / allocating routine.
+ * ONE array per GPU, shared by every context and every call: each call clears it first, and calls that
+ * overlap on the same GPU (other contexts / streams / host threads) race on it -- serialise them. */
+int epv_suffstats_static(epv_ctx *ctx, double *J, double *D);
+int epv_static_limits(uint64_t *max_nodes, uint64_t *scratch_bytes);
 /* epv_suffstats in two halves: enqueue the pass / read the result (so that a driver of several
  * contexts has all of them running before it waits for the first). */
 int epv_suffstats_async(epv_ctx *ctx);
