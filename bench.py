@@ -394,13 +394,20 @@ def main():
     avg_launch_ms = mh_ms / max(1, mh_launches)
     achieved = bytes_per_launch / (avg_launch_ms * 1e-3) / 1e9 if avg_launch_ms > 0 else 0.0
     traffic = None                      # dram bytes of the kernel from the committed ncu capture
+    traffic_source = issue_pct = lanes = None
     tfile = os.path.join(ROOT, "profiles", "r01_traffic.json")
     if os.path.exists(tfile):
         tj = json.load(open(tfile))
         if tj.get("workload") == args.workload and tj.get("n_sites_per_gpu") == args.sites:
             traffic = tj["traffic_bytes_per_launch"]
+            traffic_source = ("ncu --set full capture of the same kernel and workload, committed as profiles/r01_traffic.json "
+                              "(from profiles/r01_ncu_summary_v8_mh_update.txt); NOT measured in this run")
+            issue_pct, lanes = tj.get("issue_active_pct"), tj.get("lanes_per_inst")
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": traffic, "kernel": "mh_update_kernel",
+                "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_source,
+                # what actually bounds the kernel (same capture): issue slots used, active lanes per instruction
+                "issue_active_pct": issue_pct, "lanes_per_inst": lanes,
+                "kernel": "mh_update_kernel",
                 "peak_source": peak_src, "avg_launch_ms": avg_launch_ms, "launches_timed": mh_launches,
                 "algorithmic_bytes_per_launch": bytes_per_launch, "jumps_per_row": jbar,
                 "kernel_share_of_step": mh_ms / ms if ms > 0 else None,

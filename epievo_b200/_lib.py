@@ -109,6 +109,7 @@ SIGNATURES = {
     "epv_pathfile_write": (C.c_int, [C.c_char_p, u64, u64, C.POINTER(C.c_char_p), u8p, u64p, dp, dp, C.c_int]),
     "epv_io_last_error": (C.c_char_p, []),
     "epv_launch_count": (u64, [ctx_p]),
+    "epv_recovery_count": (u64, [ctx_p]),
     "epv_mh_kernel_time": (C.c_int, [ctx_p, C.c_int, dp, u64p]),
     "epv_rebuild_kernel_time": (C.c_int, [ctx_p, dp]),
     "epv_enable_kernel_timing": (C.c_int, [ctx_p, C.c_int]),

@@ -21,6 +21,7 @@ void free_paths(epv_ctx *c) {
     cudaFree(c->d_jmp[k]); c->d_jmp[k] = nullptr;
   }
   cudaFree(c->d_jbase); cudaFree(c->d_jcap); cudaFree(c->d_state); cudaFree(c->d_tri);
+  cudaFree(c->d_jneed); c->d_jneed = nullptr;
   cudaFree(c->d_desc); cudaFree(c->d_hcnt); cudaFree(c->d_hjmp);
   c->halo_k = HALO_K_MIN;
   cudaFree(c->d_stage_init); cudaFree(c->d_stage_off); cudaFree(c->d_stg_off); cudaFree(c->d_stg);

@@ -1,5 +1,6 @@
 // api_paths.cu -- host exchange format <-> device CSR, capacity management.
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 #include "../../include/epievo_b200.h"
@@ -26,6 +27,9 @@ int read_branch_totals(epv_ctx *c, std::vector<uint64_t> &tot) {
 static uint64_t capacity_for(uint64_t count, uint64_t n_sites) {
   // room for the stationary fluctuation of the total plus growth between checks
   uint64_t cap = count + count/2 + n_sites/16 + 4096;
+  // test-only: almost no headroom at upload, so that growth must go through the recovery of one_pass
+  static const bool tight = std::getenv("EPIEVO_B200_TIGHT_CAPACITY") != nullptr;
+  if (tight) cap = count/2 + count/32 + 64;            // (callers pass 2 x the fill)
   return (cap + 15) & ~15ull;
 }
 
@@ -45,10 +49,38 @@ static int alloc_jumps(epv_ctx *c, const std::vector<uint64_t> &cap, double *out
 // Staging blob for the accepted proposals of ONE colour pass: at most one header per
 // group (ceil(n_br/4) words of u16 counts) plus the new jump times of a third of the rows
 // (sized at half of the total jump capacity).
+// Global scratch for proposals longer than the update kernel's per-thread buffer (16 / 32 / 64 / 128 jump
+// times by tree size): one slot per overflowing site of a pass.  Sized from the data: when a site's whole-tree
+// proposal is expected to exceed half of that buffer, most sites overflow -> a slot per group, of 4 x the
+// expectation + 64; otherwise a small pool of long slots.
+static int ensure_scratch(epv_ctx *c, double t_sum, double r_mean) {
+  const int maxj = c->n_nodes <= 8 ? 16 : c->n_nodes <= 16 ? 32 : c->n_nodes <= 64 ? 64 : 128;
+  const double expect = std::max(c->jumps_per_row*(double)(c->n_nodes - 1), t_sum*r_mean);
+  uint64_t slots, cap;
+  if (2.0*expect > (double)maxj) { slots = c->n_groups + 64; cap = ((uint64_t)(4.0*expect) + 64 + 15) & ~15ull; if (cap < 256) cap = 256; }
+  else { slots = std::max<uint64_t>(2048, c->n_groups/64); cap = 2048; }
+  if (cap > 0x7fffffffull || slots > 0xfffffff0ull) return fail(c, "proposal scratch too large; use more shards");
+  if (slots*cap <= (uint64_t)c->scratch_slots*c->scratch_cap && cap <= c->scratch_cap) return 0;
+  cudaFree(c->d_scratch); c->d_scratch = nullptr;
+  EPV_CUDA(c, cudaMalloc(&c->d_scratch, slots*cap*sizeof(double)));
+  c->scratch_slots = (uint32_t)slots; c->scratch_cap = (uint32_t)cap;
+  return 0;
+}
+
 int alloc_stage(epv_ctx *c) {
   const uint64_t n_br = c->n_nodes - 1;
   c->n_groups = (c->n_sites + 2)/3;
-  const unsigned long long cap = c->n_groups*((n_br + 3)/4) + c->jmp_total_cap/2 + 4096;
+  // jump times of one pass: half of the stored capacity, or twice what a third of the sites holds at
+  // stationarity (sum of the branch lengths x the mean triplet rate per site) -- histories that start with
+  // few jumps (epievo_initialization's heuristic paths) grow towards that within a sweep
+  double t_sum = 0.0, r_mean = 1.0;
+  for (int v = 1; v < c->n_nodes; ++v) t_sum += c->h_branch[v];
+  if (c->have_model) { r_mean = 0.0; for (int i = 0; i < 8; ++i) r_mean += c->mp.rate[i]/8.0; if (r_mean < 1.0) r_mean = 1.0; }
+  if (int r = ensure_scratch(c, t_sum, c->have_model ? 1.0 : 0.0)) return r;
+  const unsigned long long model_jumps = (unsigned long long)(2.0*r_mean*t_sum*(double)c->n_groups);
+  const unsigned long long cap = c->n_groups*((n_br + 3)/4) + std::max<unsigned long long>(c->jmp_total_cap/2, model_jumps) + 4096;
+  if (cap >= 0xfffffff0ull)
+    return fail(c, "the proposal staging of one pass would exceed 2^32 words on one GPU; use more shards");
   if (c->d_stg && cap <= c->stg_cap) return 0;
   cudaFree(c->d_stg); c->d_stg = nullptr;
   EPV_CUDA(c, cudaMalloc(&c->d_stg, cap*sizeof(double)));
@@ -58,16 +90,23 @@ int alloc_stage(epv_ctx *c) {
   return 0;
 }
 
-// Grow any branch whose fill exceeds 3/4 of its capacity (called between sweeps).
-int maybe_regrow(epv_ctx *c, const std::vector<uint64_t> &tot) {
+// Thin headroom = a pass could overflow a branch: more than half full, or less room than 1.5 x what the
+// branch holds at stationarity (about one change per site per unit time).  one_pass then checks the error
+// flag after every pass and recovers (regrow + rerun of the rebuild) instead of once per sweep.
+void update_guard(epv_ctx *c, const std::vector<uint64_t> &tot) {
+  bool g = false;
+  for (size_t bi = 0; bi < tot.size(); ++bi) {
+    const double expect = 1.5*(double)c->n_own()*c->h_branch[bi + 1];
+    if (2*tot[bi] > c->h_jcap[bi] || expect > (double)c->h_jcap[bi]) g = true;
+  }
+  c->guard = g;
+}
+
+// New jump buffers with the given capacities (>= the current ones); the CURRENT buffer's contents (tot[b]
+// jumps per branch) are carried over.  keep_stage: leave the proposal staging alone (it is in use).
+int regrow_to(epv_ctx *c, const std::vector<uint64_t> &cap, const std::vector<uint64_t> &tot, bool keep_stage) {
   const int n_br = c->n_nodes - 1;
-  bool need = false;
-  for (int bi = 0; bi < n_br; ++bi)
-    if (tot[bi] > 0xfffffff0ull) return fail(c, "a branch holds more than 2^32 jumps on one GPU; use more shards");
-    else if (4*tot[bi] > 3*c->h_jcap[bi]) need = true;
-  if (!need) return 0;
-  std::vector<uint64_t> cap(n_br), base;
-  for (int bi = 0; bi < n_br; ++bi) cap[bi] = std::max(c->h_jcap[bi], capacity_for(2*tot[bi], c->n_own()));
+  std::vector<uint64_t> base;
   double *nj[2]; uint64_t total;
   if (int r = alloc_jumps(c, cap, nj, base, total)) return r;
   for (int bi = 0; bi < n_br; ++bi)
@@ -79,8 +118,23 @@ int maybe_regrow(epv_ctx *c, const std::vector<uint64_t> &tot) {
   cudaFree(c->d_jmp[0]); cudaFree(c->d_jmp[1]);
   c->d_jmp[0] = nj[0]; c->d_jmp[1] = nj[1];
   c->h_jbase = base; c->h_jcap = cap; c->jmp_total_cap = total;
-  return alloc_stage(c);
+  update_guard(c, tot);
+  return keep_stage ? 0 : alloc_stage(c);
 }
+
+// Grow any branch that is more than half full to three times its fill (called between sweeps).
+int maybe_regrow(epv_ctx *c, const std::vector<uint64_t> &tot) {
+  const int n_br = c->n_nodes - 1;
+  bool need = false;
+  for (int bi = 0; bi < n_br; ++bi)
+    if (tot[bi] > 0xfffffff0ull) return fail(c, "a branch holds more than 2^32 jumps on one GPU; use more shards");
+    else if (2*tot[bi] > c->h_jcap[bi]) need = true;
+  if (!need) { update_guard(c, tot); return alloc_stage(c); }
+  std::vector<uint64_t> cap(n_br);
+  for (int bi = 0; bi < n_br; ++bi) cap[bi] = std::max(c->h_jcap[bi], capacity_for(2*tot[bi], c->n_own()));
+  return regrow_to(c, cap, tot, false);
+}
+
 
 }  // namespace epv
 
@@ -167,6 +221,8 @@ int ensure_shape(epv_ctx *c, uint64_t n_sites) {
     EPV_CUDA(c, cudaMalloc(&c->d_off[k], (size_t)n_br*c->off_pitch*sizeof(uint32_t)));
   EPV_CUDA(c, cudaMalloc(&c->d_jbase, n_br*sizeof(uint64_t)));
   EPV_CUDA(c, cudaMalloc(&c->d_jcap, n_br*sizeof(uint64_t)));
+  EPV_CUDA(c, cudaMalloc(&c->d_jneed, n_br*sizeof(unsigned long long)));
+  EPV_CUDA(c, cudaMemsetAsync(c->d_jneed, 0, n_br*sizeof(unsigned long long), c->stream));
   EPV_CUDA(c, cudaMalloc(&c->d_state, (size_t)n_sites*c->W));
   EPV_CUDA(c, cudaMalloc(&c->d_tri, n_sites*sizeof(double)));
   EPV_CUDA(c, cudaMalloc(&c->d_desc, (size_t)n_br*c->n_tiles*sizeof(unsigned long long)));
@@ -187,15 +243,16 @@ int ensure_jumps(epv_ctx *c, const std::vector<uint64_t> &count) {
   for (int bi = 0; bi < n_br; ++bi) sum += count[bi];
   c->jumps_per_row = (double)sum/((double)n_br*(double)c->n_own());
   bool fits = (int)c->h_jcap.size() == n_br && c->d_jmp[0];
-  for (int bi = 0; fits && bi < n_br; ++bi) fits = 4*count[bi] <= 3*c->h_jcap[bi];
+  for (int bi = 0; fits && bi < n_br; ++bi) fits = 2*count[bi] <= c->h_jcap[bi];
   for (int bi = 0; bi < n_br; ++bi)
     if (count[bi] > 0xfffffff0ull) return fail(c, "a branch holds more than 2^32 jumps on one GPU; use more shards");
-  if (fits) return 0;
+  if (fits) { update_guard(c, count); return alloc_stage(c); }
   for (int k = 0; k < 2; ++k) { cudaFree(c->d_jmp[k]); c->d_jmp[k] = nullptr; }
   std::vector<uint64_t> cap(n_br);
-  for (int bi = 0; bi < n_br; ++bi) cap[bi] = capacity_for(count[bi], c->n_own());
+  for (int bi = 0; bi < n_br; ++bi) cap[bi] = capacity_for(2*count[bi], c->n_own());
   if (int r = alloc_jumps(c, cap, c->d_jmp, c->h_jbase, c->jmp_total_cap)) return r;
   c->h_jcap = cap;
+  update_guard(c, count);
   if (int r = alloc_stage(c)) return r;
   EPV_CUDA(c, cudaMemcpyAsync(c->d_jbase, c->h_jbase.data(), n_br*sizeof(uint64_t), cudaMemcpyHostToDevice, c->stream));
   EPV_CUDA(c, cudaMemcpyAsync(c->d_jcap, c->h_jcap.data(), n_br*sizeof(uint64_t), cudaMemcpyHostToDevice, c->stream));

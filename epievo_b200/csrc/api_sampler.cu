@@ -10,6 +10,8 @@ using namespace epv;
 namespace epv {
 int read_branch_totals(epv_ctx *c, std::vector<uint64_t> &tot);
 int maybe_regrow(epv_ctx *c, const std::vector<uint64_t> &tot);
+int regrow_to(epv_ctx *c, const std::vector<uint64_t> &cap, const std::vector<uint64_t> &tot, bool keep_stage);
+int alloc_stage(epv_ctx *c);
 }
 
 namespace {
@@ -43,6 +45,7 @@ void drain_timing(epv_ctx *c) {
 }
 
 int do_reset(epv_ctx *c) {
+  if (int r = alloc_stage(c)) return r;        // the staging is sized from the model, which may be newer than the paths
   launch_tri_llh(c->mp, c->view(c->cur), c->d_state, c->W, c->tree(), c->n_sites, c->d_tri, c->stream);
   ++c->launches;
   c->tri_valid = true;
@@ -64,7 +67,7 @@ int one_pass(epv_ctx *c, int colour, uint64_t seed, uint32_t sweep, const IndepL
   a.mp = c->mp;
   a.in = c->view(c->cur);
   a.off_out = c->d_off[c->cur ^ 1]; a.jmp_out = c->d_jmp[c->cur ^ 1];
-  a.jcap = c->d_jcap;
+  a.jcap = c->d_jcap; a.jneed = c->d_jneed;
   a.state = c->d_state; a.W = c->W; a.tree = c->tree(); a.tri_llh = c->d_tri;
   a.n_sites = c->n_sites; a.upd_lo = c->upd_lo(); a.upd_hi = c->upd_hi();
   a.global0 = c->global0(); a.n_global = c->n_global;
@@ -112,6 +115,40 @@ int one_pass(epv_ctx *c, int colour, uint64_t seed, uint32_t sweep, const IndepL
   c->launches += n_upd + 1;
   if (!indep) ++c->mh_launches;
   c->ticket_base += c->n_tiles;
+  // Thin headroom (or the site-independent resampling, whose rows can grow several-fold): look at the error
+  // word now.  A rebuild that overflowed a branch wrote nothing usable, but its inputs -- the CSR the pass
+  // read and the staging blob -- are intact and it recorded the totals it needs: regrow, rerun the rebuild.
+  if (c->guard || indep) {
+    for (int attempt = 0; attempt < 4; ++attempt) {
+      unsigned flags = 0;
+      EPV_CUDA(c, cudaMemcpyAsync(c->h_mail, c->d_err, sizeof(unsigned), cudaMemcpyDeviceToHost, c->stream));
+      EPV_CUDA(c, cudaStreamSynchronize(c->stream));
+      flags = *reinterpret_cast<unsigned *>(c->h_mail);
+      if (!(flags & ERR_JUMP_CAPACITY)) break;
+      const int n_br = c->n_nodes - 1;
+      std::vector<unsigned long long> need(n_br);
+      EPV_CUDA(c, cudaMemcpy(need.data(), c->d_jneed, n_br*sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+      std::vector<uint64_t> tot;                                 // fill of the INPUT CSR (c->cur is still the input)
+      if (int r = read_branch_totals(c, tot)) return r;
+      std::vector<uint64_t> cap(n_br);
+      for (int bi = 0; bi < n_br; ++bi) {
+        if (need[bi] > 0xfffffff0ull) return fail(c, "a branch holds more than 2^32 jumps on one GPU; use more shards");
+        const uint64_t want = need[bi] ? 3*need[bi] + c->n_own()/16 + 4096 : 0;
+        cap[bi] = std::max<uint64_t>(c->h_jcap[bi], (want + 15) & ~15ull);
+      }
+      if (int r = regrow_to(c, cap, tot, true)) return r;
+      flags &= ~ERR_JUMP_CAPACITY;
+      EPV_CUDA(c, cudaMemcpy(c->d_err, &flags, sizeof(unsigned), cudaMemcpyHostToDevice));
+      EPV_CUDA(c, cudaMemset(c->d_jneed, 0, n_br*sizeof(unsigned long long)));
+      ++c->epoch;
+      a.in = c->view(c->cur);
+      a.jmp_out = c->d_jmp[c->cur ^ 1];
+      a.epoch = c->epoch; a.ticket_base = c->ticket_base;
+      launch_csr_rebuild(a, c->stream);
+      c->ticket_base += c->n_tiles;
+      ++c->launches; ++c->recoveries;
+    }
+  }
   c->cur ^= 1;
   c->stats_valid = false;
   return 0;
@@ -379,6 +416,7 @@ int epv_mcem_iteration(epv_ctx *c, uint64_t burn_in, uint64_t batch, uint64_t se
 }
 
 uint64_t epv_launch_count(const epv_ctx *c) { return c ? c->launches : 0; }
+uint64_t epv_recovery_count(const epv_ctx *c) { return c ? c->recoveries : 0; }
 
 int epv_enable_kernel_timing(epv_ctx *c, int on) {
   if (!c) return 1;

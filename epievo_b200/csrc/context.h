@@ -29,6 +29,9 @@ struct epv_ctx {
   uint32_t *d_off[2] = {nullptr, nullptr};
   double *d_jmp[2] = {nullptr, nullptr};
   uint64_t *d_jbase = nullptr, *d_jcap = nullptr;
+  unsigned long long *d_jneed = nullptr;     // [n_br] written by a rebuild that overflowed (kernels.h)
+  bool guard = false;                        // thin headroom: check (and recover) after every pass, not every sweep
+  uint64_t recoveries = 0;
   std::vector<uint64_t> h_jbase, h_jcap;
   uint64_t jmp_total_cap = 0;
   int cur = 0;

@@ -15,6 +15,7 @@ struct PassArgs {
   uint32_t *off_out;          // rebuilt CSR (ping-pong partner), same pitch / jbase
   double *jmp_out;
   const uint64_t *jcap;       // [n_branches] capacity of each branch's jump slice
+  unsigned long long *jneed;  // [n_branches] on overflow: the total the rebuilt branch needs (atomicMax)
   uint8_t *state;             // in place: only the updated site's own bits change
   int W;
   TreeDev tree;

@@ -382,7 +382,10 @@ csr_rebuild_kernel(const PassArgs a) {
     const uint32_t tot = __shfl_sync(0xffffffffu, incl, 31);
     const uint32_t base = tile_base(a.desc + (uint64_t)bi*a.n_tiles, tile, a.epoch, tot, lane);
     if (lane == 0 && (uint64_t)base + tot > a.jcap[bi]) {
+      // nothing of this tile is written; the scan goes on, so the last tile records the branch's new total
+      // and the host can regrow and rerun the rebuild (its inputs are intact)
       atomicOr(a.err, ERR_JUMP_CAPACITY);
+      atomicMax(a.jneed + bi, (unsigned long long)base + tot);
       s_fail = 1;
     }
     uint32_t run = base + incl - mine;

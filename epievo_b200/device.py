@@ -339,6 +339,9 @@ class Context:
     def launch_count(self) -> int:
         return int(self.lib.epv_launch_count(self.h))
 
+    def recovery_count(self) -> int:
+        return int(self.lib.epv_recovery_count(self.h))
+
     def enable_kernel_timing(self, on: bool):
         self._ck(self.lib.epv_enable_kernel_timing(self.h, int(on)))
 

@@ -357,6 +357,11 @@ const char *epv_io_last_error(void);
 /* ---- instrumentation ------------------------------------------------------------- */
 /* Kernel launches issued by this context since creation (bench "gpu_launches"). */
 uint64_t epv_launch_count(const epv_ctx *ctx);
+/* How often a colour pass outgrew a branch's jump storage and was recovered (storage regrown, the CSR
+ * rebuild rerun from its intact inputs).  The reference's vector<double> rows are unbounded
+ * (Path.hpp:33-57); here capacity is 3 x the fill and is checked after every pass while headroom is thin
+ * (a branch more than half full, or holding less than 1.5 x its stationary expectation), else per sweep. */
+uint64_t epv_recovery_count(const epv_ctx *ctx);
 /* Device time (ms, CUDA events on the context's stream) and launch count of the
  * colour-pass update kernel (mh_update_kernel) accumulated since the last call with
  * reset != 0; epv_rebuild_kernel_time returns the csr_rebuild_kernel time accumulated

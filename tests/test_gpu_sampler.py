@@ -145,3 +145,75 @@ def test_deferred_overflow_launch_gives_the_same_chain(model, case, n, density, 
     a, b = out
     assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and a[2] == b[2]
     assert a[3].same_as(b[3]) and np.array_equal(a[4], b[4])
+
+
+@pytest.mark.parametrize("case,T", [("pair", 3.0), ("pair", 20.0), ("testtree_x10", None)])
+def test_growth_beyond_the_jump_capacity_is_recovered(cpu, model, case, T):
+    """Histories that start with 0/1 jumps per row on long branches (the heuristic starting paths of
+    epievo_initialization / MCMC_test.cpp:219-237) grow several-fold within the first sweeps: a colour pass
+    then outgrows the jump storage sized at upload.  The rebuild's inputs are intact, so the library regrows
+    and reruns it (epv_recovery_count) instead of failing with "jump storage capacity exceeded".
+    EPIEVO_B200_TIGHT_CAPACITY (test-only) sizes the storage at upload with 3 % headroom so that the growth
+    certainly goes through that path; the chain must equal the one of a run with the normal headroom."""
+    from epievo_b200.device import Context
+    from epievo_b200.paths import PathSet, parse_newick
+    rates, Tm = model
+    tree = Tree.pair(T) if case == "pair" else parse_newick("((C:0.3,D:0.6)E:0.2,F:1.0)G:0.0;")
+    n = 30000
+    rng = np.random.default_rng(2)
+    # every node's sequence: a coarse random pattern; a branch gets one jump where its two ends differ
+    seq = [(rng.random(n) < 0.5).astype(np.uint8) for _ in range(tree.n_nodes)]
+    rows, init = [[[] for _ in range(n)]], [np.zeros(n, np.uint8)]
+    for v in range(1, tree.n_nodes):
+        a = seq[int(tree.parent_ids[v])]
+        u = rng.random(n)*float(tree.branches[v])
+        rows.append([[u[s]] if a[s] != seq[v][s] else [] for s in range(n)])
+        init.append(a)
+    tot = np.array(tree.branches, np.float64); tot[0] = 0.0
+    ps = PathSet.from_rows(n, tree.n_nodes, init, rows, tot)
+    outs = []
+    for rep in range(2):
+        c = Context(0)
+        try:
+            c.set_tree(tree); c.set_model(rates, Tm); c.upload_paths(ps); c.reset()
+            J, D, acc = c.run_mcmc(6, 2, seed=4)
+            out = c.download_paths()
+            assert out.jumps.size > 1.5*ps.jumps.size
+            cached = c.tri_llh()
+            outs.append((J, D, acc, out))
+        finally:
+            c.close()
+    check_valid(tree, ps, outs[0][3])
+    cpu.load_paths(outs[0][3])
+    assert rel_close(cached, cpu.tri_llh(rates, Tm), 1e-9, atol=1e-12)
+    # time is conserved, and the run is reproducible
+    assert np.allclose(outs[0][1][1:].sum(1), (n - 2)*np.asarray(tree.branches)[1:], rtol=1e-9)
+    assert outs[0][3].same_as(outs[1][3]) and np.array_equal(outs[0][0], outs[1][0])
+    # the same problem in a fresh process with tight storage: recovered, and the same chain
+    import json, subprocess, sys, tempfile, os
+    with tempfile.TemporaryDirectory() as tmp:
+        np.savez(os.path.join(tmp, "in.npz"), init=ps.init_state, off=ps.row_off, jumps=ps.jumps, tot=ps.tot_time,
+                 ss=tree.subtree_sizes, par=tree.parent_ids, br=tree.branches, rates=rates, T=Tm)
+        code = (
+            "import sys, json, numpy as np\n"
+            "sys.path.insert(0, %r)\n"
+            "from epievo_b200.device import Context\n"
+            "from epievo_b200.paths import PathSet, Tree\n"
+            "d = np.load(%r)\n"
+            "tree = Tree(d['ss'], d['par'], d['br'], ['n%%d' %% i for i in range(len(d['br']))])\n"
+            "n = len(d['init'])//tree.n_nodes\n"
+            "ps = PathSet(n, tree.n_nodes, d['init'], d['off'], d['jumps'], d['tot'])\n"
+            "c = Context(0); c.set_tree(tree); c.set_model(d['rates'], d['T']); c.upload_paths(ps); c.reset()\n"
+            "J, D, acc = c.run_mcmc(6, 2, seed=4)\n"
+            "out = c.download_paths()\n"
+            "np.savez(%r, jumps=out.jumps, off=out.row_off, init=out.init_state, J=J)\n"
+            "print(json.dumps({'recoveries': c.recovery_count()}))\n"
+        ) % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))), os.path.join(tmp, "in.npz"), os.path.join(tmp, "out.npz"))
+        env = dict(os.environ, EPIEVO_B200_TIGHT_CAPACITY="1")
+        r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env)
+        assert r.returncode == 0, r.stderr[-2000:]
+        assert json.loads(r.stdout.strip().splitlines()[-1])["recoveries"] > 0, "the recovery path was not exercised"
+        got = np.load(os.path.join(tmp, "out.npz"))
+        ref = outs[0][3]
+        assert np.array_equal(got["off"], ref.row_off) and np.array_equal(got["jumps"], ref.jumps)
+        assert np.array_equal(got["init"], ref.init_state) and np.array_equal(got["J"], outs[0][0])
