@@ -60,7 +60,11 @@ static int ensure_scratch(epv_ctx *c, double t_sum, double r_mean) {
   if (2.0*expect > (double)maxj) { slots = c->n_groups + 64; cap = ((uint64_t)(4.0*expect) + 64 + 15) & ~15ull; if (cap < 256) cap = 256; }
   else { slots = std::max<uint64_t>(2048, c->n_groups/64); cap = 2048; }
   if (cap > 0x7fffffffull || slots > 0xfffffff0ull) return fail(c, "proposal scratch too large; use more shards");
-  if (slots*cap <= (uint64_t)c->scratch_slots*c->scratch_cap && cap <= c->scratch_cap) return 0;
+  if (slots <= c->scratch_slots && cap <= c->scratch_cap) return 0;
+  slots = std::max<uint64_t>(slots, c->scratch_slots); cap = std::max<uint64_t>(cap, c->scratch_cap);
+  if (slots > c->n_groups + 64 && cap > 256) {       // the small pool of long slots became a slot per group: shorter slots
+    cap = ((uint64_t)(4.0*expect) + 64 + 15) & ~15ull; if (cap < 256) cap = 256;
+  }
   cudaFree(c->d_scratch); c->d_scratch = nullptr;
   EPV_CUDA(c, cudaMalloc(&c->d_scratch, slots*cap*sizeof(double)));
   c->scratch_slots = (uint32_t)slots; c->scratch_cap = (uint32_t)cap;

@@ -127,7 +127,8 @@ int one_pass(epv_ctx *c, int colour, uint64_t seed, uint32_t sweep, const IndepL
       if (!(flags & ERR_JUMP_CAPACITY)) break;
       const int n_br = c->n_nodes - 1;
       std::vector<unsigned long long> need(n_br);
-      EPV_CUDA(c, cudaMemcpy(need.data(), c->d_jneed, n_br*sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+      EPV_CUDA(c, cudaMemcpyAsync(need.data(), c->d_jneed, n_br*sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+      EPV_CUDA(c, cudaStreamSynchronize(c->stream));
       std::vector<uint64_t> tot;                                 // fill of the INPUT CSR (c->cur is still the input)
       if (int r = read_branch_totals(c, tot)) return r;
       std::vector<uint64_t> cap(n_br);
@@ -138,8 +139,9 @@ int one_pass(epv_ctx *c, int colour, uint64_t seed, uint32_t sweep, const IndepL
       }
       if (int r = regrow_to(c, cap, tot, true)) return r;
       flags &= ~ERR_JUMP_CAPACITY;
-      EPV_CUDA(c, cudaMemcpy(c->d_err, &flags, sizeof(unsigned), cudaMemcpyHostToDevice));
-      EPV_CUDA(c, cudaMemset(c->d_jneed, 0, n_br*sizeof(unsigned long long)));
+      EPV_CUDA(c, cudaMemcpyAsync(c->d_err, &flags, sizeof(unsigned), cudaMemcpyHostToDevice, c->stream));
+      EPV_CUDA(c, cudaMemsetAsync(c->d_jneed, 0, n_br*sizeof(unsigned long long), c->stream));
+      EPV_CUDA(c, cudaStreamSynchronize(c->stream));
       ++c->epoch;
       a.in = c->view(c->cur);
       a.jmp_out = c->d_jmp[c->cur ^ 1];

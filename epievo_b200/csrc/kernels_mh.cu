@@ -84,8 +84,12 @@ __host__ __device__ constexpr int mh_qcap(int maxn) { return maxn <= 16 ? 8 : ma
 // Shared memory of the update kernel, in this order: jump queue [MH_THREADS*QCAP] QSlot, prefix counts
 // [MH_THREADS] int, then (lockstep routine, trees up to 64 nodes) TreeTab [n_nodes], BranchTab [n_nodes],
 // jump counts per node u16 [n_nodes][MH_THREADS], q of the internal nodes f64 [2*slots][MH_THREADS].
+#ifndef EPV_JBASE_SMEM
+#define EPV_JBASE_SMEM 0
+#endif
 struct MhShared {
   QSlot *queue; int *excl; TreeTab *tt; BranchTab *bt; uint16_t *pn; double *q; uint16_t *poff;
+  const uint64_t *jbase;
 };
 template <int MAXN>
 __host__ __device__ inline size_t mh_smem_layout(int n_nodes, int q_slots, size_t *off /*[7]*/) {
@@ -126,6 +130,9 @@ mh_update_group(const PassArgs &a, const ModelParams &s_mp, const CtxTables &s_t
   const bool active = g < a.n_groups && st >= a.upd_lo && st < a.upd_hi && gsite >= 1 &&
                       gsite + 1 < (int64_t)a.n_global;
   SiteCtx c; c.pv = a.in; c.state = a.state; c.W = a.W; c.tree = a.tree; c.site = st;
+#if EPV_JBASE_SMEM
+  c.pv.jbase = sh.jbase;                 // the branches' slice starts from shared memory (a dependent load per row access)
+#endif
   constexpr bool MIX = mh_impl(MAXN) == 2;
   if constexpr (LOCK) {
     typename std::conditional<MIX, MixScratch<MAXN, PB, QCAP, QSMEM>, LockScratch<MAXN, PB, QCAP, QSMEM> >::type S;
@@ -185,10 +192,18 @@ mh_update_group(const PassArgs &a, const ModelParams &s_mp, const CtxTables &s_t
     S.queue = sh.queue + t*QCAP; S.excl = sh.excl + (t & ~31);
     int r = mh_site_flat<MAXN, PB, QCAP, HALO>(active, a.coop != 0, s_mp, s_tb, c, a.state, a.tri_llh, a.seed, a.sweep,
                                                (uint64_t)gsite, a.n_global, S, pr, total);
-    const bool generic = r == -3;
+    if (DEFER) {
+      // the main launch of a long pass: a site the flat routine cannot finish goes to the overflow list
+      // (second, small launch of the full routine below); the main kernel carries no fallback code
+      if (r == -1 || r == -3) {
+        a.ovf_list[1 + atomicAdd(a.ovf_list, 1u)] = (uint32_t)g;
+        deferred = true; r = 0;
+      }
+    }
+    const bool generic = !DEFER && r == -3;
     if (generic)
       r = mh_site(s_mp, c, a.state, a.tri_llh, a.seed, a.sweep, (uint64_t)gsite, a.n_global, S.q, pr, total);
-    if (__any_sync(0xffffffffu, r == -1)) {
+    if (!DEFER && __any_sync(0xffffffffu, r == -1)) {
       const bool again = r == -1;
       if (again) {
         const uint32_t slot = atomicAdd(a.scratch_ctr, 1u);
@@ -252,6 +267,10 @@ mh_update_kernel(const PassArgs a, int q_slots) {
   __shared__ CtxTables s_tb;
   extern __shared__ __align__(16) unsigned char s_dyn[];
   const int t = threadIdx.x;
+#if EPV_JBASE_SMEM
+  __shared__ uint64_t s_jbase[MAXN];
+  for (int i = t; i < a.tree.n_nodes - 1; i += MH_THREADS) s_jbase[i] = a.in.jbase[i];
+#endif
   if (t == 0) s_mp = a.mp;
   fill_tables(a.mp, s_tb, t);
   MhShared sh;
@@ -262,6 +281,11 @@ mh_update_kernel(const PassArgs a, int q_slots) {
     sh.tt = reinterpret_cast<TreeTab *>(s_dyn + off[2]); sh.bt = reinterpret_cast<BranchTab *>(s_dyn + off[3]);
     sh.pn = reinterpret_cast<uint16_t *>(s_dyn + off[4]); sh.q = reinterpret_cast<double *>(s_dyn + off[5]);
     sh.poff = reinterpret_cast<uint16_t *>(s_dyn + off[6]);
+#if EPV_JBASE_SMEM
+    sh.jbase = s_jbase;
+#else
+    sh.jbase = a.in.jbase;
+#endif
   }
   __syncthreads();
   if (mh_lock(MAXN)) {

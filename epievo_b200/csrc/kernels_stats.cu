@@ -252,8 +252,20 @@ constexpr int ST_QCAP = 168;     // < 32 left over + up to 130 new entries per (
 #endif
 __device__ __forceinline__ void prefetch_l1(const void *p) { asm volatile("prefetch.global.L1 [%0];" :: "l"(p)); }
 
+// ST_SPLIT_ (default): the 40-bit fixed-point event times go to the bins as three 14-bit pieces with native
+// 32-bit shared atomics (RED, fire and forget); a 64-bit shared atomicAdd is a compare-and-swap spin loop on
+// this architecture (ATOMS.CAST.SPIN.64) and was a third of the kernel's instructions.  A piece bin holds
+// 2^18 adds; every lane counts its adds and after 1024 (256 lanes x 1024 = 2^18) goes on in the 64-bit
+// bins, so the sums stay exact whatever the data.
+#ifndef ST_SPLIT_
+#define ST_SPLIT_ 1
+#endif
+constexpr unsigned ST_LANE_ADDS = 1024;
+
 struct TileShared {
-  long long *S;        // [n_br*24*cols] fixed-point sums of event times, class = trip_before*3 + which
+  long long *S;        // ST_SPLIT_: [n_br*24] 64-bit overflow bins; else [n_br*24*cols] fixed-point sums of event
+                       // times, class = trip_before*3 + which
+  unsigned *P;         // ST_SPLIT_: [n_br*24*cols][3] sums of the 14-bit pieces
   unsigned *J;         // [n_br*8]
   unsigned *C;         // [n_br*8] rows by final triplet
   double *scale;       // [n_br] SS_FIX / tot_time
@@ -275,11 +287,28 @@ load_step(const uint32_t *ob, int lane) {      // ob = the branch's offset of th
   return r;
 }
 
+// One event time into the bin of (branch, class).
+__device__ __forceinline__ void
+bin_add(const TileShared &T, int bi, int cls, int col, unsigned long long v, unsigned &n_adds) {
+#if ST_SPLIT_
+  if (n_adds < ST_LANE_ADDS) {
+    unsigned *p = T.P + 3*((((size_t)bi*24 + cls) << T.col_shift) + col);
+    atomicAdd(p, (unsigned)(v & 0x3fffu));
+    atomicAdd(p + 1, (unsigned)((v >> 14) & 0x3fffu));
+    atomicAdd(p + 2, (unsigned)(v >> 28));
+    ++n_adds;
+  }
+  else atomicAdd(reinterpret_cast<unsigned long long *>(T.S + bi*24 + cls), v);
+#else
+  atomicAdd(reinterpret_cast<unsigned long long *>(T.S + ((((size_t)bi*24 + cls) << T.col_shift) + col)), v);
+#endif
+}
+
 // (one call site, inlined: as an out-of-line call its by-reference arguments and the registers saved
 // around it were local-memory traffic twice the size of the kernel's global loads)
 __device__ __forceinline__ void
 st_drain(const PathView &pv, const uint8_t *state, int W, const TileShared &T, const unsigned *queue,
-         int n_take, uint64_t first_s0, uint64_t ord_stride) {
+         int n_take, uint64_t first_s0, uint64_t ord_stride, unsigned &n_adds) {
   const int lane = threadIdx.x & 31;
   __syncwarp();
   if (lane < n_take) {
@@ -303,7 +332,7 @@ st_drain(const PathView &pv, const uint8_t *state, int W, const TileShared &T, c
     const int b0 = (int)((state_word(state, W, s) >> sh) & 1);
     const double *jb = pv.jmp + pv.jbase[bi];
     const double scale = T.scale[bi];
-    long long *S = T.S + ((size_t)bi*24 << T.col_shift) + (lane & ((1 << T.col_shift) - 1));
+    const int col = lane & ((1 << T.col_shift) - 1);
     const uint32_t nl = o0 - a2, nn = nl + (e2 - o1);
     for (uint32_t k = 0; k < o1 - o0; ++k) {
       const double t = jb[o0 + k];
@@ -321,13 +350,13 @@ st_drain(const PathView &pv, const uint8_t *state, int W, const TileShared &T, c
       }
       const int x2 = b2 ^ (int)(fl & 1), x1 = b1 ^ (int)((fl >> 1) & 1), y1 = d1 ^ (int)((fl >> 2) & 1),
                 y2 = d2 ^ (int)(fl >> 3);
-      if (vL) atomicAdd(reinterpret_cast<unsigned long long *>(S + (((x2*4 + x1*2 + own)*3 + 0) << T.col_shift)), v);
+      if (vL) bin_add(T, bi, (x2*4 + x1*2 + own)*3 + 0, col, v, n_adds);
       if (vM) {
         const int tb = x1*4 + own*2 + y1;
-        atomicAdd(reinterpret_cast<unsigned long long *>(S + ((tb*3 + 1) << T.col_shift)), v);
+        bin_add(T, bi, tb*3 + 1, col, v, n_adds);
         atomicAdd(&T.J[bi*8 + tb], 1u);
       }
-      if (vR) atomicAdd(reinterpret_cast<unsigned long long *>(S + (((own*4 + y1*2 + y2)*3 + 2) << T.col_shift)), v);
+      if (vR) bin_add(T, bi, (own*4 + y1*2 + y2)*3 + 2, col, v, n_adds);
     }
   }
   __syncwarp();
@@ -339,10 +368,21 @@ suffstats_tile_kernel(const PathView pv, const uint8_t *state, int W, int n_br, 
                       uint64_t r0, uint64_t n_tiles, int col_shift, unsigned long long *acc) {
   extern __shared__ unsigned long long s_raw[];
   TileShared T;
+#if ST_SPLIT_
+  // [n_br*24] u64 overflow bins, [n_br] scales, then the piece bins (u32 x 3 per bin and column), J, C, queues
+  const int n_bins = n_br*24, n_pieces = 3*((n_br*24) << col_shift);
+  T.S = reinterpret_cast<long long *>(s_raw);
+  T.scale = reinterpret_cast<double *>(s_raw + n_bins);
+  T.P = reinterpret_cast<unsigned *>(s_raw + n_bins + n_br);
+  T.J = T.P + n_pieces;
+  for (int i = threadIdx.x; i < n_pieces; i += ST_THREADS) T.P[i] = 0;
+#else
   const int n_bins = (n_br*24) << col_shift;
   T.S = reinterpret_cast<long long *>(s_raw);
   T.scale = reinterpret_cast<double *>(s_raw + n_bins);
   T.J = reinterpret_cast<unsigned *>(s_raw + n_bins + n_br);
+  T.P = nullptr;
+#endif
   T.C = T.J + n_br*8;
   T.col_shift = col_shift;
   T.c_lo = pv.own_lo + r0; T.c_hi = T.c_lo + n_tiles*ST_ROWS;
@@ -364,6 +404,7 @@ suffstats_tile_kernel(const PathView pv, const uint8_t *state, int W, int n_br, 
   // only the last batch of a warp is partial.
   const uint64_t first_s0 = pv.own_lo + r0 + warp_id*ST_ROWS, ord_stride = n_warps*ST_ROWS;
   int qn = 0;                                    // queue fill (warp-uniform)
+  unsigned n_adds = 0;                           // this lane's adds to the piece bins (bin_add)
   TileStep cur;
   const uint32_t *p_tile = pv.off + r0 + warp_id*ST_ROWS;    // branch 0, first row of the warp's tile
 #if ST_PIPE_
@@ -430,7 +471,7 @@ suffstats_tile_kernel(const PathView pv, const uint8_t *state, int W, int n_br, 
       const bool last = bi + 1 == n_br && tile + n_warps >= n_tiles;   // this warp's last step
       while (qn >= 32 || (last && qn > 0)) {
         const int n_take = qn < 32 ? qn : 32;
-        st_drain(pv, state, W, T, s_queue + (qn - n_take), n_take, first_s0, ord_stride);
+        st_drain(pv, state, W, T, s_queue + (qn - n_take), n_take, first_s0, ord_stride, n_adds);
         qn -= n_take;
       }
     }
@@ -439,7 +480,15 @@ suffstats_tile_kernel(const PathView pv, const uint8_t *state, int W, int n_br, 
   // integer-only global accumulation; columns are summed here
   for (int i = threadIdx.x; i < n_br*24; i += ST_THREADS) {
     unsigned long long v = 0;
+#if ST_SPLIT_
+    v = (unsigned long long)T.S[i];
+    for (int cix = 0; cix < (1 << col_shift); ++cix) {
+      const unsigned *pp = T.P + 3*(((size_t)i << col_shift) + cix);
+      v += (unsigned long long)pp[0] + ((unsigned long long)pp[1] << 14) + ((unsigned long long)pp[2] << 28);
+    }
+#else
     for (int cix = 0; cix < (1 << col_shift); ++cix) v += (unsigned long long)T.S[((size_t)i << col_shift) + cix];
+#endif
     if (v) {
       const int bi = i/24, cls = i%24;
       atomicAdd(acc + bi*SS_ACC + 32 + cls, v & 0xffffffffull);
@@ -651,8 +700,13 @@ launch_suffstats(const PathView &pv, const uint8_t *state, int W, const TreeDev 
       const unsigned blocks = (unsigned)(want < wave ? want : wave);
       // bin columns: as many as fit in ~24 KB (fewer CAS retries), at least 2
       int col_shift = 5;
+#if ST_SPLIT_
+      while (col_shift > 0 && ((size_t)n_br*24*12 << col_shift) > ST_BINKB_*1024) --col_shift;
+      const size_t smem = ((size_t)n_br*24*12 << col_shift) + (size_t)n_br*24*8 + (size_t)n_br*8 + (size_t)n_br*8*(4 + 4) +
+#else
       while (col_shift > 1 && ((size_t)n_br*24*8 << col_shift) > ST_BINKB_*1024) --col_shift;
       const size_t smem = ((size_t)n_br*24*8 << col_shift) + (size_t)n_br*8 + (size_t)n_br*8*(4 + 4) +
+#endif
                           (ST_THREADS/32)*ST_QCAP*sizeof(unsigned);
       auto kernel = W <= 4 ? suffstats_tile_kernel<uint32_t> : suffstats_tile_kernel<uint64_t>;
       cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

@@ -232,7 +232,9 @@ mh_site_flat(bool active, bool coop, const ModelParams &mp, const CtxTables &tb,
   }
 
   // ---- 1. upward pruning, flat over (branch, interval) ----------------------------
-  for (int v = 0; v < n_nodes; ++v) { q[2*v] = 1.0; q[2*v + 1] = 1.0; pr.pn[v] = 0; }
+  // (an INACTIVE lane leaves its outputs alone: the caller re-enters this routine with only the lanes that
+  // need a larger proposal buffer active, and the other lanes still hold the result of their first call)
+  for (int v = 0; v < n_nodes; ++v) { q[2*v] = 1.0; q[2*v + 1] = 1.0; if (active) pr.pn[v] = 0; }
   int sp = 0;
   {
     int v = active ? n_nodes - 1 : 0;
@@ -272,7 +274,7 @@ mh_site_flat(bool active, bool coop, const ModelParams &mp, const CtxTables &tb,
 
   // ---- 2. downward pass, flat over (branch, interval) -----------------------------
   Philox rng; rng.init(seed, sweep, gsite, 1u);
-  pr.pend[0] = active ? (uint8_t)sw.bit(0, 1) : 0;
+  if (active) pr.pend[0] = (uint8_t)sw.bit(0, 1);
   int total = 0, qn = 0, q_total = 0;
   {
     int v = (active && status > 0) ? 1 : n_nodes, prev = 0, i = 0;
@@ -335,7 +337,7 @@ mh_site_flat(bool active, bool coop, const ModelParams &mp, const CtxTables &tb,
     if (total < 0) status = total;
   }
   __syncwarp(FULL);
-  total_out = total;
+  if (active) total_out = total;
 
   // ---- 4. the three triple log-likelihoods: one five-way merge per branch ----------
   const bool live = active && status > 0;
