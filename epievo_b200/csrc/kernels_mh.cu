@@ -477,6 +477,229 @@ csr_rebuild_kernel(const PassArgs a) {
   }
 }
 
+// ---- CSR re-compaction, offsets staged with the bulk-async copy engine ------------------------------------
+// Same tiles, same thread -> rows mapping, same chained scan and the same result as csr_rebuild_kernel; what
+// changes is how the offsets move.  They are 1.4 GB of the kernel's 1.8 GB of traffic and, per (tile, branch),
+// one contiguous 4 KB run: instead of two passes of dependent 16-byte loads per thread (the old kernel waits
+// 9.8 cycles per issue on the long scoreboard), one elected thread has the copy engine (cp.async.bulk +
+// mbarrier, the TMA path for linear data) bring the runs of a CHUNK of branches into shared memory while the
+// CTA works on the previous chunk; the new offsets are written in place in shared memory and go back to HBM
+// as bulk stores.  Jump times (4 % of the bytes) are copied as before.
+namespace bulk {
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, unsigned parity) {
+  asm volatile(
+    "{\n\t.reg .pred p;\n\t"
+    "WAIT_%=:\n\t"
+    "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+    "@!p bra WAIT_%=;\n\t}"
+    :: "r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// global -> shared, completion counted in bytes on the mbarrier
+__device__ __forceinline__ void load_async(void *dst_smem, const void *src_gmem, unsigned bytes, uint64_t *bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               :: "r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+// shared -> global, tracked by the issuing thread's bulk group
+__device__ __forceinline__ void store_async(void *dst_gmem, const void *src_smem, unsigned bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+               :: "l"(dst_gmem), "r"(smem_u32(src_smem)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void store_wait_read_all() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+constexpr int ROW_ELEMS = RB_TILE_ROWS + 4;       // a tile's offsets of one branch + the closing one, 16-byte multiple
+
+}  // namespace bulk
+
+// Dynamic shared memory: [2][BC][ROW_ELEMS] u32 staged offsets, [BC][RB_THREADS] u32 quad sums, [BC][8] warp-edge
+// offsets, 2 mbarriers.
+__global__ void __launch_bounds__(RB_THREADS)
+csr_rebuild_bulk_kernel(const PassArgs a, int BC) {
+  using namespace bulk;
+  extern __shared__ __align__(128) unsigned char s_raw[];
+  uint32_t *s_off = reinterpret_cast<uint32_t *>(s_raw);                        // [2][BC][ROW_ELEMS]
+  uint32_t *s_len = s_off + (size_t)2*BC*ROW_ELEMS;                             // [BC][RB_THREADS]
+  uint32_t *s_edge = s_len + (size_t)BC*RB_THREADS;                             // [BC][RB_THREADS/32]
+  uint64_t *s_bar = reinterpret_cast<uint64_t *>(s_edge + (size_t)BC*(RB_THREADS/32));   // [2]
+  __shared__ uint32_t s_tile;
+  __shared__ int s_fail;
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int n_br = a.tree.n_nodes - 1;
+  if (t == 0) {
+    s_tile = atomicAdd(a.ticket, 1u) - a.ticket_base;   // tile order = scheduling order
+    s_fail = 0;
+    mbar_init(&s_bar[0], 1); mbar_init(&s_bar[1], 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+  const uint32_t tile = s_tile;
+  const uint64_t own_lo = a.in.own_lo, n_own = a.in.own_hi - own_lo;
+  const uint64_t R0 = (uint64_t)tile*RB_TILE_ROWS, R = R0 + 4*(uint64_t)t;
+  const int hw = stage_header_words(n_br);
+  const int n_chunks = (n_br + BC - 1)/BC;
+  // elements of a branch's offsets to stage (never past the branch's pitch) and to store back
+  // (rows < n_own, the closing offset, rounded up to the quad: what the old kernel's threads with R <= n_own write)
+  const unsigned load_elems = (unsigned)((a.in.off_pitch - R0) < (uint64_t)ROW_ELEMS ? (a.in.off_pitch - R0) : (uint64_t)ROW_ELEMS);
+  const unsigned store_elems = R0 + RB_TILE_ROWS <= n_own ? (unsigned)RB_TILE_ROWS : (unsigned)(((n_own - R0) & ~3ull) + 4);
+
+  auto issue_loads = [&](int chunk) {        // thread 0 only
+    const int s = chunk & 1, b0 = chunk*BC, nb = min(BC, n_br - b0);
+    mbar_expect_tx(&s_bar[s], (unsigned)nb*load_elems*4u);
+    for (int u = 0; u < nb; ++u)
+      load_async(s_off + ((size_t)s*BC + u)*ROW_ELEMS, a.in.off + (uint64_t)(b0 + u)*a.in.off_pitch + R0, load_elems*4u, &s_bar[s]);
+  };
+  if (t == 0) issue_loads(0);
+
+
+  // the (at most two) rows of the quad whose site has this pass's colour: row k0 and, when k0 == 0, row 3
+  const int k0 = (int)((a.colour + 3 - (int)((R + own_lo) % 3)) % 3);
+  bool acc0 = false, acc1 = false;
+  const uint16_t *cnt0 = nullptr, *cnt1 = nullptr;
+  const double *pj0 = nullptr, *pj1 = nullptr;
+  if (R + k0 < n_own) {
+    const uint32_t so = a.stage_off[(R + k0 + own_lo)/3];
+    acc0 = so != STG_REJECTED;
+    if (so < STG_EMPTY) { cnt0 = reinterpret_cast<const uint16_t *>(a.stage + so); pj0 = a.stage + so + hw; }
+  }
+  if (k0 == 0 && R + 3 < n_own) {
+    const uint32_t so = a.stage_off[(R + 3 + own_lo)/3];
+    acc1 = so != STG_REJECTED;
+    if (so < STG_EMPTY) { cnt1 = reinterpret_cast<const uint16_t *>(a.stage + so); pj1 = a.stage + so + hw; }
+  }
+  int poff0 = 0, poff1 = 0;
+
+  for (int chunk = 0; chunk < n_chunks; ++chunk) {
+    const int s = chunk & 1, b0 = chunk*BC, nb = min(BC, n_br - b0);
+    // the other stage was stored from by chunk-1: its bulk stores must have READ shared memory before the copy
+    // engine overwrites it with chunk+1 (all threads left chunk-1 at the barrier that closed it)
+    if (t == 0 && chunk + 1 < n_chunks) { store_wait_read_all(); issue_loads(chunk + 1); }
+    // staged jump counts of this chunk's branches (global loads, issued before the wait)
+    uint32_t c0[8], c1[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      c0[u] = 0; c1[u] = 0;
+      if (u < nb) { if (cnt0) c0[u] = cnt0[b0 + u]; if (cnt1) c1[u] = cnt1[b0 + u]; }
+    }
+    mbar_wait(&s_bar[s], (unsigned)((chunk >> 1) & 1));
+    uint32_t *so_base = s_off + (size_t)s*BC*ROW_ELEMS;
+
+    // ---- new row lengths of the quad, summed per thread ------------------------------------------------
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      if (u >= nb) break;
+      uint32_t sum = 0;
+      const uint32_t *o = so_base + (size_t)u*ROW_ELEMS + 4*t;
+      const uint32_t e = o[4];
+      if (lane == 31) s_edge[u*(RB_THREADS/32) + warp] = e;     // the next warp's first offset, kept for the write phase
+      if (R < n_own) {
+        const uint4 q = *reinterpret_cast<const uint4 *>(o);
+        uint32_t len[4] = {q.y - q.x, q.z - q.y, q.w - q.z, e - q.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          if (R + k >= n_own) len[k] = 0;
+          if (k < 3 && k == k0 && acc0) len[k] = c0[u];
+          if (k == 3 && acc1) len[k] = c1[u];
+          sum += len[k];
+        }
+      }
+      s_len[u*RB_THREADS + t] = sum;
+    }
+    __syncthreads();
+
+    // ---- per-branch tile scan + chained look-back: one warp per branch of the chunk (BC <= 8) --------------
+    constexpr int PER = RB_THREADS/32;
+    if (warp < nb) {
+      const int bi = b0 + warp;
+      uint32_t *row = s_len + warp*RB_THREADS;
+      uint32_t v[PER], mine = 0;
+#pragma unroll
+      for (int k = 0; k < PER; ++k) { v[k] = row[lane*PER + k]; mine += v[k]; }
+      uint32_t incl = mine;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t up = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += up;
+      }
+      const uint32_t tot = __shfl_sync(0xffffffffu, incl, 31);
+      const uint32_t base = tile_base(a.desc + (uint64_t)bi*a.n_tiles, tile, a.epoch, tot, lane);
+      if (lane == 0 && (uint64_t)base + tot > a.jcap[bi]) {
+        // nothing more of this tile is written; the scans go on (later tiles wait for every branch's
+        // descriptor), so the last tile records the branch's new total and the host can regrow and rerun
+        atomicOr(a.err, ERR_JUMP_CAPACITY);
+        atomicMax(a.jneed + bi, (unsigned long long)base + tot);
+        s_fail = 1;
+      }
+      uint32_t run = base + incl - mine;
+#pragma unroll
+      for (int k = 0; k < PER; ++k) { row[lane*PER + k] = run; run += v[k]; }
+    }
+    __syncthreads();
+    const bool write = !s_fail;
+
+    // ---- the rebuilt rows: jump times to HBM, offsets IN PLACE in shared memory ---------------------------------
+    // A thread owns elements 4t..4t+3 of the staged run; the fifth input (the next quad's first offset) comes
+    // from the neighbouring lane's registers, or from s_edge across a warp boundary, so no thread reads an
+    // element another thread overwrites.
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      if (u >= nb) break;
+      const int bi = b0 + u;
+      uint32_t *o = so_base + (size_t)u*ROW_ELEMS + 4*t;
+      const uint4 q = *reinterpret_cast<const uint4 *>(o);
+      uint32_t e = __shfl_down_sync(0xffffffffu, q.x, 1);
+      if (lane == 31) e = s_edge[u*(RB_THREADS/32) + warp];
+      if (!write || R > n_own) continue;
+      uint32_t w = s_len[u*RB_THREADS + t];
+      uint32_t out[4] = {w, w, w, w};                  // R == n_own: the closing offset
+      if (R < n_own) {
+        const uint32_t in[5] = {q.x, q.y, q.z, q.w, e};
+        const uint64_t jb = a.in.jbase[bi];
+        const double *src_base = a.in.jmp + jb;
+        double *dst_base = a.jmp_out + jb;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          out[k] = w;
+          if (R + k >= n_own) continue;
+          if (k < 3 && k == k0 && acc0) {
+            const int n_new = (int)c0[u];
+            for (int x = 0; x < n_new; ++x) dst_base[w + x] = pj0[poff0 + x];
+            poff0 += n_new; w += n_new;
+          }
+          else if (k == 3 && acc1) {
+            const int n_new = (int)c1[u];
+            for (int x = 0; x < n_new; ++x) dst_base[w + x] = pj1[poff1 + x];
+            poff1 += n_new; w += n_new;
+          }
+          else {
+            const uint32_t n = in[k + 1] - in[k];
+            for (uint32_t x = 0; x < n; ++x) dst_base[w + x] = src_base[in[k] + x];
+            w += n;
+          }
+        }
+      }
+      *reinterpret_cast<uint4 *>(o) = make_uint4(out[0], out[1], out[2], out[3]);
+    }
+    fence_async_smem();               // the generic-proxy writes above, before the copy engine reads them
+    __syncthreads();
+    if (t == 0 && write) {
+      for (int u = 0; u < nb; ++u)
+        store_async(a.off_out + (uint64_t)(b0 + u)*a.in.off_pitch + R0, so_base + (size_t)u*ROW_ELEMS, store_elems*4u);
+      store_commit();
+    }
+  }
+  if (t == 0) store_wait_read_all();   // shared memory must outlive the copy engine's reads
+}
+
 }  // namespace
 
 size_t
@@ -585,8 +808,32 @@ launch_mh_pass(const PassArgs &a, cudaStream_t st) {
   return n + launch_mh_edge(a, st);
 }
 
+// EPIEVO_B200_REBUILD=bulk[:BC] selects the bulk-staged kernel (BC = branches per chunk, 1..8); the default is
+// the kernel with per-thread loads.  (Read once; an experiment switch, not an API.)
+static int
+rebuild_bulk_chunk(int n_br) {
+  static int mode = -2;
+  if (mode == -2) {
+    const char *e = getenv("EPIEVO_B200_REBUILD");
+    mode = -1;
+    if (e && !strncmp(e, "bulk", 4)) mode = e[4] == ':' ? atoi(e + 5) : 0;
+  }
+  if (mode < 0) return 0;
+  int bc = mode > 0 ? mode : 4;
+  bc = bc > 8 ? 8 : bc;
+  return bc > n_br ? n_br : bc;
+}
+
 void
 launch_csr_rebuild(const PassArgs &a, cudaStream_t st) {
+  const int n_br = a.tree.n_nodes - 1;
+  if (const int bc = rebuild_bulk_chunk(n_br)) {
+    const size_t smem = ((size_t)2*bc*bulk::ROW_ELEMS + (size_t)bc*RB_THREADS + (size_t)bc*(RB_THREADS/32))*sizeof(uint32_t)
+                      + 2*sizeof(uint64_t);
+    cudaFuncSetAttribute(csr_rebuild_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    csr_rebuild_bulk_kernel<<<a.n_tiles, RB_THREADS, smem, st>>>(a, bc);
+    return;
+  }
   const size_t smem = mh_pass_smem_bytes(a.tree.n_nodes);
   // branches whose loads are grouped: measured best 2 for 14 branches (1.03 vs 1.07 / 1.13 ms at
   // 1 / 4), 4 for 62 (1.52 vs 1.67 / 1.60 ms at 1 / 2)

@@ -8,18 +8,18 @@ timeout 400 $TR --master-port 29511 tools/dist_check.py > gpurun_out/r02_dist_ch
 grep -E "BIT-EXACT|MISMATCH|rc=" gpurun_out/r02_dist_check_n$N.txt
 # 2. weak scaling, headline shard per GPU, overlapped exchange (and the serial one for comparison at N=2, 8)
 timeout 600 $TR --master-port 29512 bench.py --gpus $N --no-cpu-baseline > gpurun_out/r02_bench_bal8_weak_n$N.json 2> gpurun_out/r02_bench_bal8_weak_n$N.err
-python -c "import json; d=json.load(open('gpurun_out/r02_bench_bal8_weak_n$N.json')); print('weak bal8 n=$N', d['value'], d['ms_per_step'], d['e2e']['value'], d['mcem_iter']['ms'])"
-if [ "$N" = "2" ] || [ "$N" = "8" ]; then
+python tools/show_bench.py gpurun_out/r02_bench_bal8_weak_n$N.json
+if [ "$N" = "2" ]; then
   timeout 600 $TR --master-port 29513 bench.py --gpus $N --no-cpu-baseline --no-e2e --no-mcem --serial-exchange > gpurun_out/r02_bench_bal8_weak_serial_n$N.json 2> gpurun_out/r02_bench_bal8_weak_serial_n$N.err
-  python -c "import json; d=json.load(open('gpurun_out/r02_bench_bal8_weak_serial_n$N.json')); print('weak bal8 serial n=$N', d['value'], d['ms_per_step'])"
+  python tools/show_bench.py gpurun_out/r02_bench_bal8_weak_serial_n$N.json
 fi
 # 3. config 4 as written: 3e7 sites in total, strong scaling
 timeout 600 $TR --master-port 29514 bench.py --gpus $N --workload testtree --scaling strong --sites 30000000 --no-cpu-baseline > gpurun_out/r02_bench_c4_strong_n$N.json 2> gpurun_out/r02_bench_c4_strong_n$N.err
-python -c "import json; d=json.load(open('gpurun_out/r02_bench_c4_strong_n$N.json')); print('strong C4 n=$N', d['value'], d['ms_per_step'], d['e2e']['value'], d['mcem_iter']['ms'])"
+python tools/show_bench.py gpurun_out/r02_bench_c4_strong_n$N.json
 if [ "$N" = "8" ]; then
   # 4. config 5 at its stated shape: 32-leaf tree, 1e8 sites, -B 100 -L 20, -b, 8 GPUs (histories generated on the device)
   timeout 900 $TR --master-port 29515 bench.py --gpus 8 --workload bal32 --scaling strong --sites 100000000 --burn-in 20 --batch 100 --steps 1 --warmup 1 --optimize-branches --gen device --no-cpu-baseline > gpurun_out/r02_bench_c5_n8.json 2> gpurun_out/r02_bench_c5_n8.err
-  python -c "import json; d=json.load(open('gpurun_out/r02_bench_c5_n8.json')); print('C5 n=8', d['value'], d['ms_per_step'], d['mcem_iter'])"
+  python tools/show_bench.py gpurun_out/r02_bench_c5_n8.json
   tail -3 gpurun_out/r02_bench_c5_n8.err
 fi
 if [ "$N" = "2" ]; then

@@ -108,3 +108,28 @@ def test_est_complete_param_file_from_product_m_step(lib):
     lib.epv_estimate_rates(ps.n_nodes, _d(J.reshape(-1).copy()), _d(D.reshape(-1).copy()), 1e-10,
                            _d(r), _d(T), _d(bl))
     assert fmt_params(T, bl) == open(os.path.join(CLI, "est_complete.param")).read()
+
+
+def test_multi_partition_matches_the_python_driver():
+    """epv_multi_partition (csrc/api_multi.cu, the C++ drop-in's sharding) == epievo_b200.sharded.partition:
+    contiguous blocks that cover the sites, starts multiples of 3, at least 6 sites each."""
+    import ctypes as C
+
+    import numpy as np
+
+    from epievo_b200 import _lib as L
+    from epievo_b200 import sharded as S
+    lib = L.load()
+    for n, w in ((100, 3), (1001, 8), (12, 2), (10**8, 8), (3*10**7, 4), (47, 7)):
+        b, e = np.zeros(w, np.uint64), np.zeros(w, np.uint64)
+        rc = lib.epv_multi_partition(n, w, b.ctypes.data_as(L.u64p), e.ctypes.data_as(L.u64p))
+        try:
+            want = S.partition(n, w)
+        except ValueError:
+            assert rc != 0
+            continue
+        assert rc == 0
+        assert [(int(x), int(y)) for x, y in zip(b, e)] == want
+        assert b[0] == 0 and e[-1] == n and all(int(x) % 3 == 0 for x in b)
+    b, e = np.zeros(4, np.uint64), np.zeros(4, np.uint64)
+    assert lib.epv_multi_partition(20, 4, b.ctypes.data_as(L.u64p), e.ctypes.data_as(L.u64p)) != 0   # < 6 sites per shard
