@@ -24,6 +24,7 @@ import os
 import subprocess
 import sys
 import tempfile
+import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
@@ -65,16 +66,48 @@ class ClockSampler:
                 stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
+        self._start_nvml()
+
+    # A timed region shorter than nvidia-smi's first report (strong scaling at N=8: 3 steps of 57 ms) would end
+    # with no sample at all: the same counters are also read in-process through NVML every 10 ms.
+    def _start_nvml(self):
+        self.nvml, self.nvml_stop, self.nvml_thread = [], threading.Event(), None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            mx = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+            bits = (("hw_slowdown", pynvml.nvmlClocksEventReasonHwSlowdown),
+                    ("hw_thermal_slowdown", pynvml.nvmlClocksEventReasonHwThermalSlowdown),
+                    ("sw_thermal_slowdown", pynvml.nvmlClocksEventReasonSwThermalSlowdown),
+                    ("sw_power_cap", pynvml.nvmlClocksEventReasonSwPowerCap))
+
+            def loop():
+                while not self.nvml_stop.is_set():
+                    try:
+                        sm = float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM))
+                        r = int(pynvml.nvmlDeviceGetCurrentClocksEventReasons(h))
+                        self.nvml.append((sm, mx, [nm for nm, b in bits if r & b]))
+                    except Exception:
+                        pass
+                    self.nvml_stop.wait(0.01)
+
+            self.nvml_thread = threading.Thread(target=loop, daemon=True)
+            self.nvml_thread.start()
+        except Exception:
+            self.nvml_thread = None
 
     def stop(self):
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        if self.proc is None:
-            return out
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except Exception:
-            self.proc.kill()
+        if getattr(self, "nvml_thread", None) is not None:
+            self.nvml_stop.set()
+            self.nvml_thread.join(timeout=2)
+        if self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         try:
@@ -93,6 +126,11 @@ class ClockSampler:
             os.unlink(self.path)
         except Exception:
             pass
+        out["source"] = "nvidia-smi"
+        if not sm and self.nvml:
+            out["source"] = "nvml"
+            for a, b, r in self.nvml:
+                sm.append(a); mx.append(b); reasons.update(r)
         if sm:
             sm.sort()
             out.update(sm_mhz=sm[len(sm) // 2], sm_max_mhz=max(mx), samples=len(sm))

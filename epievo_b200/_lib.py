@@ -53,6 +53,7 @@ SIGNATURES = {
     "epv_halo_unpack": (C.c_int, [ctx_p, C.c_int, C.c_void_p, C.c_void_p]),
     "epv_halo_capacity": (C.c_int, [ctx_p, u64p, u64p]),
     "epv_halo_set_capacity": (C.c_int, [ctx_p, u64]),
+    "epv_halo_need_async": (C.c_int, [ctx_p, C.c_void_p, C.c_void_p]),
     "epv_set_side_stream": (C.c_int, [ctx_p, C.c_void_p]),
     "epv_pass_begin": (C.c_int, [ctx_p, C.c_int, u64, u64, C.c_void_p, C.c_void_p]),
     "epv_pass_end": (C.c_int, [ctx_p, C.c_int, C.c_void_p, C.c_void_p]),

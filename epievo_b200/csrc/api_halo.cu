@@ -50,6 +50,17 @@ int epv_halo_capacity(epv_ctx *c, uint64_t *capacity, uint64_t *needed) {
   return 0;
 }
 
+int epv_halo_need_async(epv_ctx *c, void *dst_device, void *stream) {
+  if (!c) return 1;
+  if (!c->n_sites) return fail(c, "no paths loaded");
+  if (!dst_device) return fail(c, "epv_halo_need_async: dst_device is required");
+  cudaSetDevice(c->device);
+  cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : c->side_stream;
+  EPV_CUDA(c, cudaMemsetAsync(dst_device, 0, sizeof(uint64_t), st));
+  EPV_CUDA(c, cudaMemcpyAsync(dst_device, c->d_hmax, sizeof(unsigned), cudaMemcpyDeviceToDevice, st));   // low word
+  return 0;
+}
+
 int epv_halo_set_capacity(epv_ctx *c, uint64_t capacity) {
   if (!c) return 1;
   if (!c->n_sites) return fail(c, "no paths loaded");

@@ -214,6 +214,10 @@ class Context:
     def halo_set_capacity(self, capacity: int):
         self._ck(self.lib.epv_halo_set_capacity(self.h, capacity))
 
+    def halo_need_async(self, dst_device_ptr: int, cuda_stream_ptr: Optional[int] = None):
+        """Longest boundary row packed so far -> one uint64 at dst_device_ptr, enqueued (no synchronisation)."""
+        self._ck(self.lib.epv_halo_need_async(self.h, C.c_void_p(dst_device_ptr), C.c_void_p(cuda_stream_ptr)))
+
     def set_side_stream(self, cuda_stream_ptr: int):
         self._ck(self.lib.epv_set_side_stream(self.h, C.c_void_p(cuda_stream_ptr)))
 

@@ -166,6 +166,12 @@ int epv_halo_unpack(epv_ctx *ctx, int colour, const void *rec_lo, const void *re
  * sweep raises an error, it is never truncated. */
 int epv_halo_capacity(epv_ctx *ctx, uint64_t *capacity, uint64_t *needed);
 int epv_halo_set_capacity(epv_ctx *ctx, uint64_t capacity);
+/* The same check without a host synchronisation (one per sweep costs a multi-process driver ~0.3 ms of idle
+ * GPU: 0.4 ms x 20 sweeps was the whole weak-scaling loss at 8 GPUs): enqueue, on `stream` (a cudaStream_t the
+ * caller has ordered after the packs; NULL = the context's side stream), a copy of the longest boundary row
+ * packed so far into *dst_device (one uint64, device memory).  The driver reduces it over shards (max), reads
+ * it a sweep later and grows with epv_halo_set_capacity when twice the value passes the capacity. */
+int epv_halo_need_async(epv_ctx *ctx, void *dst_device, void *stream);
 
 /* The same colour pass with the exchange OVERLAPPED.  epv_pass_begin enqueues, on the context's side
  * stream (epv_set_side_stream; default: an internal one), the halo-aware update of the few groups next
