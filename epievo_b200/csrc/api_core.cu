@@ -31,9 +31,11 @@ void free_paths(epv_ctx *c) {
   c->d_jbase = c->d_jcap = nullptr; c->d_state = nullptr; c->d_tri = nullptr;
   c->d_desc = nullptr;
   c->n_sites = 0; c->tri_valid = false; c->stats_valid = false; c->h_jcap.clear();
+  c->hk_pending = false;
 }
 
 int check_device_flags(epv_ctx *c) {
+  if (int r = housekeeping_take(c)) return r;      // (a record of the last sweep that nobody looked at yet)
   unsigned flags = 0;
   EPV_CUDA(c, cudaMemcpyAsync(c->h_mail, c->d_err, sizeof(unsigned), cudaMemcpyDeviceToHost, c->stream));
   EPV_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -83,6 +85,8 @@ int epv_create(epv_ctx **out, int device) {
     && cudaMalloc(&c->d_out9, 9*sizeof(double)) == cudaSuccess
     && cudaMalloc(&c->d_mail, 4096*sizeof(unsigned long long)) == cudaSuccess
     && cudaMallocHost(&c->h_mail, 4096*sizeof(unsigned long long)) == cudaSuccess
+    && cudaMallocHost(&c->h_hk, 4096*sizeof(uint32_t)) == cudaSuccess
+    && cudaEventCreateWithFlags(&c->ev_hk, cudaEventDisableTiming) == cudaSuccess
     && cudaMalloc(&c->d_scratch, (size_t)c->scratch_slots*c->scratch_cap*sizeof(double)) == cudaSuccess
     && cudaEventCreate(&c->ev0) == cudaSuccess && cudaEventCreate(&c->ev1) == cudaSuccess;
   for (int k = 0; ok && k < 3*epv_ctx::EV_RING; ++k)
@@ -119,6 +123,7 @@ void epv_destroy(epv_ctx *c) {
   cudaFree(c->d_err); cudaFree(c->d_nacc); cudaFree(c->d_ticket); cudaFree(c->d_scratch_ctr);
   cudaFree(c->d_stg_ctr); cudaFree(c->d_itab); cudaFree(c->d_iacc);
   cudaFree(c->d_scratch); cudaFree(c->d_out9); cudaFree(c->d_mail); cudaFreeHost(c->h_mail);
+  cudaFreeHost(c->h_hk); if (c->ev_hk) cudaEventDestroy(c->ev_hk);
   cudaFree(c->d_J); cudaFree(c->d_D); cudaFree(c->d_Jsum); cudaFree(c->d_Dsum); cudaFree(c->d_ss);
   cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1);
   for (int k = 0; k < 3*epv_ctx::EV_RING; ++k) if (c->ev_ring[k]) cudaEventDestroy(c->ev_ring[k]);
@@ -139,7 +144,7 @@ int epv_synchronize(epv_ctx *c) {
   if (!c) return 1;
   EPV_CUDA(c, cudaStreamSynchronize(c->stream));
   EPV_CUDA(c, cudaStreamSynchronize(c->side_stream));
-  return 0;
+  return c->n_sites ? housekeeping_take(c) : 0;
 }
 
 int epv_set_side_stream(epv_ctx *c, void *s) {

@@ -68,6 +68,10 @@ struct epv_ctx {
   // small pinned host mailbox
   unsigned long long *h_mail = nullptr;      // [64 + n_nodes]
   unsigned long long *d_mail = nullptr;
+  // per-sweep housekeeping read a sweep late (branch totals + error word copied asynchronously, api_sampler.cu)
+  uint32_t *h_hk = nullptr;                  // pinned, [1 + n_branches]
+  cudaEvent_t ev_hk = nullptr;
+  bool hk_pending = false;
 
   // halo store (rows of the <= 3 + 3 halo sites, outside the CSR; see common.cuh)
   uint16_t *d_hcnt = nullptr;               // [2*HALO_W][n_br]
@@ -113,6 +117,7 @@ int fail(epv_ctx *c, const std::string &msg);
 int check_cuda(epv_ctx *c, cudaError_t e, const char *what);
 void free_paths(epv_ctx *c);
 int check_device_flags(epv_ctx *c);
+int housekeeping_take(epv_ctx *c);     // api_sampler.cu: look at the last sweep's late housekeeping record, if any
 int set_halo_capacity(epv_ctx *c, int k);  // reallocates the halo store (contents kept)
 // pieces of the upload path shared with epv_simulate_adopt (api_paths.cu)
 int64_t slot_site(const epv_ctx *c, int k);

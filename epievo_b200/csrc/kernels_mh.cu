@@ -317,8 +317,13 @@ mh_update_kernel(const PassArgs a, int q_slots) {
 // Thread t of tile k owns the 4 consecutive CSR rows R = 4*(k*RB_THREADS + t) .. R+3 of
 // every branch (offsets move as one 16-byte vector).  Rows whose site has the pass's colour
 // take their new length / jump times from the staging blob when the update was accepted.
+#ifdef EPV_RB_MINBLOCKS         // CTAs per SM the rebuild kernel is compiled for (default: the compiler's choice)
+#define EPV_RB_BOUNDS __launch_bounds__(RB_THREADS, EPV_RB_MINBLOCKS)
+#else
+#define EPV_RB_BOUNDS __launch_bounds__(RB_THREADS)
+#endif
 template <int UNROLL>
-__global__ void __launch_bounds__(RB_THREADS)
+__global__ void EPV_RB_BOUNDS
 csr_rebuild_kernel(const PassArgs a) {
   extern __shared__ uint32_t s_len[];            // [n_branches][RB_THREADS]
   __shared__ uint32_t s_tile;

@@ -9,7 +9,7 @@ grep -E "BIT-EXACT|MISMATCH|rc=" gpurun_out/r02_dist_check_n$N.txt
 # 2. weak scaling, headline shard per GPU, overlapped exchange (and the serial one for comparison at N=2, 8)
 timeout 600 $TR --master-port 29512 bench.py --gpus $N --no-cpu-baseline > gpurun_out/r02_bench_bal8_weak_n$N.json 2> gpurun_out/r02_bench_bal8_weak_n$N.err
 python tools/show_bench.py gpurun_out/r02_bench_bal8_weak_n$N.json
-if [ "$N" = "2" ]; then
+if [ "$2" = "serial" ]; then
   timeout 600 $TR --master-port 29513 bench.py --gpus $N --no-cpu-baseline --no-e2e --no-mcem --serial-exchange > gpurun_out/r02_bench_bal8_weak_serial_n$N.json 2> gpurun_out/r02_bench_bal8_weak_serial_n$N.err
   python tools/show_bench.py gpurun_out/r02_bench_bal8_weak_serial_n$N.json
 fi
