@@ -4,8 +4,10 @@ mkdir -p gpurun_out
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
 nvidia-smi topo -m > gpurun_out/r02_topo_n$N.txt 2>&1
 # 1. N ranks over real NCCL == one GPU, bit for bit (overlapped + serial protocol, -b loop)
+if [ "$2" != "bench-only" ]; then
 timeout 400 $TR --master-port 29511 tools/dist_check.py > gpurun_out/r02_dist_check_n$N.txt 2>&1; echo "rc=$?" >> gpurun_out/r02_dist_check_n$N.txt
 grep -E "BIT-EXACT|MISMATCH|rc=" gpurun_out/r02_dist_check_n$N.txt
+fi
 # 2. weak scaling, headline shard per GPU, overlapped exchange (and the serial one for comparison at N=2, 8)
 timeout 600 $TR --master-port 29512 bench.py --gpus $N --no-cpu-baseline > gpurun_out/r02_bench_bal8_weak_n$N.json 2> gpurun_out/r02_bench_bal8_weak_n$N.err
 python tools/show_bench.py gpurun_out/r02_bench_bal8_weak_n$N.json
@@ -16,7 +18,7 @@ fi
 # 3. config 4 as written: 3e7 sites in total, strong scaling
 timeout 600 $TR --master-port 29514 bench.py --gpus $N --workload testtree --scaling strong --sites 30000000 --no-cpu-baseline > gpurun_out/r02_bench_c4_strong_n$N.json 2> gpurun_out/r02_bench_c4_strong_n$N.err
 python tools/show_bench.py gpurun_out/r02_bench_c4_strong_n$N.json
-if [ "$N" = "8" ]; then
+if [ "$N" = "8" ] && [ "$2" != "bench-only" ]; then
   # 4. config 5 at its stated shape: 32-leaf tree, 1e8 sites, -B 100 -L 20, -b, 8 GPUs (histories generated on the device)
   timeout 900 $TR --master-port 29515 bench.py --gpus 8 --workload bal32 --scaling strong --sites 100000000 --burn-in 20 --batch 100 --steps 1 --warmup 1 --optimize-branches --gen device --no-cpu-baseline > gpurun_out/r02_bench_c5_n8.json 2> gpurun_out/r02_bench_c5_n8.err
   python tools/show_bench.py gpurun_out/r02_bench_c5_n8.json
