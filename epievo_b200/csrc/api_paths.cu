@@ -154,6 +154,19 @@ int read_halo_store(epv_ctx *c, std::vector<uint16_t> &cnt, std::vector<double> 
   return 0;
 }
 
+// Row capacity of the halo store for boundary rows of up to kmax jumps now: twice that, and four times what a
+// row of the longest branch holds at stationarity (about 1.5 changes per unit time, as update_guard) -- histories
+// that start short on long branches (T = 20) grow several-fold in their first sweeps, before any regrow rule,
+// read late or not, has seen them.
+int halo_capacity_for(const epv_ctx *c, uint64_t kmax) {
+  double t_max = 0.0;
+  for (int b = 1; b < c->n_nodes; ++b) t_max = std::max(t_max, c->h_branch[b]);
+  // test-only: no headroom over the rows present, so that growth has to come from the between-sweeps check
+  if (std::getenv("EPIEVO_B200_TIGHT_HALO")) return (int)std::max<uint64_t>(HALO_K_MIN, kmax + 8);
+  const double want = std::max({(double)HALO_K_MIN, 2.0*(double)kmax + 16.0, 6.0*t_max + 16.0});
+  return (int)std::min(want, 60000.0);
+}
+
 // Halo rows hold up to k jumps each from now on (k only grows); the store's contents are kept.
 int set_halo_capacity(epv_ctx *c, int k) {
   k = (k + 7) & ~7;
@@ -307,7 +320,7 @@ int epv_upload_paths(epv_ctx *c, uint64_t n_sites, uint64_t n_nodes, const uint8
         if (c->halo_hi) kmax = std::max(kmax, row_off[r + n_sites - d] - row_off[r + n_sites - d - 1]);
       }
     if (kmax > 30000) return fail(c, "a shard-boundary row holds more than 30000 jumps");
-    if (int r = set_halo_capacity(c, std::max<int>(HALO_K_MIN, 2*(int)kmax + 16))) return r;
+    if (int r = set_halo_capacity(c, halo_capacity_for(c, kmax))) return r;
   }
   const size_t HK = c->halo_k;
   std::vector<uint16_t> hc((size_t)2*HALO_W*n_br, 0);
@@ -469,7 +482,7 @@ int epv_upload_paths_compact(epv_ctx *c, uint64_t n_sites, uint64_t n_nodes, con
       }
     }
     if (kmax > 30000) return fail(c, "a shard-boundary row holds more than 30000 jumps");
-    if (int r = set_halo_capacity(c, std::max<int>(HALO_K_MIN, 2*(int)kmax + 16))) return r;
+    if (int r = set_halo_capacity(c, halo_capacity_for(c, kmax))) return r;
   }
   const size_t HK = c->halo_k;
   std::vector<uint16_t> hc((size_t)2*HALO_W*n_br, 0);
