@@ -538,5 +538,18 @@ def main():
     return 0
 
 
+def _quiet_stdout():
+    """stdout must carry exactly ONE line, the JSON record: libraries write there at will (NCCL prints its
+    version on rank 0 at the first collective).  File descriptor 1 is pointed at stderr for the whole run and
+    Python's sys.stdout at a copy of the original descriptor, so only this script's own print reaches it."""
+    sys.stdout.flush()
+    keep = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(keep, "w", buffering=1)
+
+
 if __name__ == "__main__":
-    sys.exit(main())
+    _quiet_stdout()
+    rc = main()
+    sys.stdout.flush()
+    sys.exit(rc)

@@ -218,6 +218,7 @@ int check_upload(epv_ctx *c, uint64_t n_sites, uint64_t n_nodes, const double *t
   // new paths: a device-side failure of the previous ones (sticky flags) no longer applies
   EPV_CUDA(c, cudaMemsetAsync(c->d_err, 0, sizeof(unsigned), c->stream));
   EPV_CUDA(c, cudaMemsetAsync(c->d_hmax, 0, sizeof(unsigned), c->stream));
+  c->hk_pending = false;                 // a late housekeeping record of the previous paths means nothing now
   return 0;
 }
 
