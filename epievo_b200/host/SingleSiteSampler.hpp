@@ -95,6 +95,12 @@ get_sufficient_statistics(const std::vector<std::vector<Path> > &all_paths,
                           const TreeHelper &th,
                           std::vector<std::vector<double> > &J,
                           std::vector<std::vector<double> > &D);
+/* The reference's own signature (no tree: J/D are per branch and do not depend on the topology);
+ * host/ParamEstimation_b200.cpp makes it the link-time replacement of the reference's function. */
+void
+get_sufficient_statistics(const std::vector<std::vector<Path> > &all_paths,
+                          std::vector<std::vector<double> > &J,
+                          std::vector<std::vector<double> > &D);
 }
 
 #endif

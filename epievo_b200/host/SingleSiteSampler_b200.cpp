@@ -91,11 +91,13 @@ for_site_ranges(size_t n_sites, size_t n_threads, F f) {
   for (size_t t = 0; t < th.size(); ++t) th[t].join();
 }
 
-/* [site][node] -> node-major CSR (the order of the local-paths file, Path.cpp:123-148) */
-void
-SingleSiteSampler::upload(const vector<vector<Path> > &paths, const TreeHelper &th) {
-  const size_t n_sites = paths.size(), n_nodes = th.n_nodes;
-  const double t0 = now_s();
+/* [site][node] -> node-major CSR (the order of the local-paths file, Path.cpp:123-148), threaded over
+ * site ranges: every thread first counts the jumps of its rows per node, then writes them where they go. */
+template <typename Off>
+static void
+flatten_paths(const vector<vector<Path> > &paths, const size_t n_nodes, vector<unsigned char> &init_state,
+              vector<Off> &row_off, vector<double> &jumps, vector<double> &tot_time) {
+  const size_t n_sites = paths.size();
   init_state.assign(n_sites*n_nodes, 0);
   row_off.assign(n_sites*n_nodes + 1, 0);
   tot_time.assign(n_nodes, 0.0);
@@ -123,6 +125,13 @@ SingleSiteSampler::upload(const vector<vector<Path> > &paths, const TreeHelper &
     }
   });
   row_off[n_sites*n_nodes] = total;
+}
+
+void
+SingleSiteSampler::upload(const vector<vector<Path> > &paths, const TreeHelper &th) {
+  const size_t n_sites = paths.size(), n_nodes = th.n_nodes;
+  const double t0 = now_s();
+  flatten_paths(paths, n_nodes, init_state, row_off, jumps, tot_time);
   const double t1 = now_s();
   check(epv_multi_upload_paths(ctx, n_sites, n_nodes, init_state.data(),
                                reinterpret_cast<const uint64_t *>(row_off.data()), jumps.data(),
@@ -206,34 +215,27 @@ SingleSiteSampler::run_mcmc(const EpiEvoModel &the_model, const TreeHelper &th,
 
 namespace epievo_b200 {
 
-/* get_sufficient_statistics per branch (ParamEstimation.cpp:92-114) on the GPU. */
-void
-get_sufficient_statistics(const vector<vector<Path> > &all_paths, const TreeHelper &th,
-                          vector<vector<double> > &J, vector<vector<double> > &D) {
+/* get_sufficient_statistics per branch (ParamEstimation.cpp:92-114) on the GPU.  The topology does not enter
+ * the statistics (they are per branch); ss / pi only have to describe SOME tree in preorder. */
+static void
+suffstats_on_device(const vector<vector<Path> > &all_paths, const size_t n_nodes,
+                    const vector<uint64_t> &ss, const vector<uint64_t> &pi,
+                    vector<vector<double> > &J, vector<vector<double> > &D) {
   // a throw-away context: tree + paths only (no model needed for J/D)
   epv_ctx *c = nullptr;
   if (epv_create(&c, int_from_env("EPIEVO_B200_DEVICE", 0)) != 0 || !c)
     throw std::runtime_error("epievo_b200: no usable CUDA device (there is no CPU fallback)");
   struct Guard { epv_ctx *c; ~Guard() { epv_destroy(c); } } guard{c};
   auto ck = [&](int rc) { if (rc) throw std::runtime_error(std::string("epievo_b200: ") + epv_last_error(c)); };
-  const size_t n_sites = all_paths.size(), n_nodes = th.n_nodes;
-  vector<uint64_t> ss(th.subtree_sizes.begin(), th.subtree_sizes.end());
-  vector<uint64_t> pi(th.parent_ids.begin(), th.parent_ids.end());
+  const size_t n_sites = all_paths.size();
+  if (n_sites < 3 || n_nodes < 2) throw std::runtime_error("epievo_b200: need at least 3 sites and one branch");
   vector<double> br(n_nodes, 0.0);
   for (size_t b = 1; b < n_nodes; ++b) br[b] = all_paths[0][b].tot_time;   // rows carry the time
   ck(epv_set_tree(c, n_nodes, ss.data(), pi.data(), br.data()));
-  vector<unsigned char> init(n_sites*n_nodes, 0);
-  vector<uint64_t> off(n_sites*n_nodes + 1, 0);
-  vector<double> jmp;
-  for (size_t b = 1; b < n_nodes; ++b)
-    for (size_t s2 = 0; s2 < n_sites; ++s2) {
-      const Path &p = all_paths[s2][b];
-      init[b*n_sites + s2] = p.init_state;
-      off[b*n_sites + s2] = jmp.size();
-      jmp.insert(jmp.end(), p.jumps.begin(), p.jumps.end());
-    }
-  off[n_sites*n_nodes] = jmp.size();
-  if (jmp.empty()) jmp.push_back(0.0);
+  vector<unsigned char> init;
+  vector<uint64_t> off;
+  vector<double> jmp, tot;
+  flatten_paths(all_paths, n_nodes, init, off, jmp, tot);
   ck(epv_upload_paths(c, n_sites, n_nodes, init.data(), off.data(), jmp.data(), br.data()));
   vector<double> Jf(n_nodes*8), Df(n_nodes*8);
   ck(epv_suffstats(c, Jf.data(), Df.data()));
@@ -241,6 +243,24 @@ get_sufficient_statistics(const vector<vector<Path> > &all_paths, const TreeHelp
   D.assign(n_nodes, vector<double>(8, 0.0));
   for (size_t b = 1; b < n_nodes; ++b)
     for (size_t t = 0; t < 8; ++t) { J[b][t] = Jf[b*8 + t]; D[b][t] = Df[b*8 + t]; }
+}
+
+void
+get_sufficient_statistics(const vector<vector<Path> > &all_paths, const TreeHelper &th,
+                          vector<vector<double> > &J, vector<vector<double> > &D) {
+  vector<uint64_t> ss(th.subtree_sizes.begin(), th.subtree_sizes.end());
+  vector<uint64_t> pi(th.parent_ids.begin(), th.parent_ids.end());
+  suffstats_on_device(all_paths, th.n_nodes, ss, pi, J, D);
+}
+
+void
+get_sufficient_statistics(const vector<vector<Path> > &all_paths,
+                          vector<vector<double> > &J, vector<vector<double> > &D) {
+  if (all_paths.empty()) throw std::runtime_error("epievo_b200: no paths");
+  const size_t n_nodes = all_paths[0].size();
+  vector<uint64_t> ss(n_nodes, 1), pi(n_nodes, 0);       // a star: every node hangs off the root
+  ss[0] = n_nodes;
+  suffstats_on_device(all_paths, n_nodes, ss, pi, J, D);
 }
 
 }  // namespace epievo_b200

@@ -132,3 +132,23 @@ def test_epievo_initialization_b200(tmp_path):
         p_ks = stats.ks_2samp(gold[:, k], rows[:, k]).pvalue
         p_t = stats.ttest_ind(gold[:, k], rows[:, k], equal_var=False).pvalue
         assert min(p_ks, p_t) > 1e-3/8, (name, p_ks, p_t, gold[:, k].mean(), rows[:, k].mean())
+
+
+def test_est_complete_b200_writes_the_reference_parameter_file(tmp_path):
+    """Config 3's program: `epievo_est_complete` (J/D pass over every path + M-step) compiled unchanged and
+    linked with host/ParamEstimation_b200.cpp, which replaces get_sufficient_statistics / estimate_rates on
+    paths at link time.  No RNG on this path: the parameter file must be the one the CPU reference binary wrote
+    (tests/golden/cli/est_complete.param) -- identical text, or (D goes through 2^-40 fixed point on the
+    device) every number within 1e-9 relative."""
+    exe = need("epievo_est_complete_b200")
+    par = str(tmp_path / "c.param")
+    r = subprocess.run([exe, "-v", "-o", par, os.path.join(CLI, "test.param"), os.path.join(CLI, "tree.nwk"),
+                        os.path.join(CLI, "sim.paths")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert "[COMPUTING INITIAL SUFFICIENT STATISTICS]" in r.stderr          # the replaced function ran
+    got, want = open(par).read(), open(os.path.join(CLI, "est_complete.param")).read()
+    if got != want:
+        g = [float(x) for l in got.splitlines() for x in l.split()[1:]]
+        w = [float(x) for l in want.splitlines() for x in l.split()[1:]]
+        assert [l.split()[0] for l in got.splitlines()] == [l.split()[0] for l in want.splitlines()]
+        assert np.allclose(g, w, rtol=1e-9, atol=0), (got, want)

@@ -5,6 +5,8 @@
       input: `epievo_sim -s 1 -n 10000` -> `global_jumps_to_paths`, by the reference binaries (BASELINE config 1)
   C1M the same program on a 10^6-site local-paths file (histories from the library's simulator, written by
       epv_pathfile_write): reference `-i 1` (one iteration, ~2 minutes), drop-in `-i 1` and `-i 10`
+  C3  `epievo_est_complete` (J/D pass over every path + M-step; BASELINE config 3's program) on the same 10^6-site
+      file: the drop-in replaces get_sufficient_statistics / estimate_rates on paths at link time
   C2  `epievo_sim_pairwise -T 1.0 -L 10 -s 3` on 10^6 sites (root + leaf columns of `epievo_sim -s 2 -T 1.0`)
 
 The drop-in's own phases come from EPIEVO_B200_TIMING=1 (flatten / upload / device / download / unflatten,
@@ -100,6 +102,12 @@ def main():
         out["C1M_est_params_histories_1e6_sites_1_iteration"] = res
         out["C1M_est_params_histories_1e6_sites_10_iterations"] = pair("epievo_est_params_histories", base, tmp,
                                                                        gpus=gp, ref=False)
+        # ---- C3-like: epievo_est_complete (J/D pass + M-step, no sampling) on the same 10^6-site file --
+        c3 = [PARAM, TREE, tmp + "/m.paths"]
+        res = pair("epievo_est_complete", c3, tmp)
+        res["speedup"] = round(res["reference"]["wall_s"]/res["b200"]["wall_s"], 2)
+        res["same_parameter_file"] = open(tmp + "/ref.out").read() == open(tmp + "/b200.out").read()
+        out["C3_est_complete_1e6_sites"] = res
         del ps
 
         # ---- C2: pairwise, 10^6 sites, T = 1 ----------------------------------------------------------
