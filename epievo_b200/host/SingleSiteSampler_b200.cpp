@@ -26,13 +26,13 @@ int_from_env(const char *name, int dflt) {
  * is destroyed (tools/cli_bench.py reads it). */
 namespace {
 struct PhaseClock {
-  double flatten = 0, upload = 0, device = 0, download = 0, unflatten = 0;
+  double create = 0, flatten = 0, upload = 0, device = 0, download = 0, unflatten = 0;
   size_t calls = 0;
   const bool on = std::getenv("EPIEVO_B200_TIMING") != nullptr;
   ~PhaseClock() {
     if (on && calls)
-      std::fprintf(stderr, "[epievo_b200 timing] calls=%zu flatten=%.4f upload=%.4f device=%.4f download=%.4f unflatten=%.4f\n",
-                   calls, flatten, upload, device, download, unflatten);
+      std::fprintf(stderr, "[epievo_b200 timing] calls=%zu create=%.4f flatten=%.4f upload=%.4f device=%.4f download=%.4f unflatten=%.4f\n",
+                   calls, create, flatten, upload, device, download, unflatten);
   }
 } phase_clock;
 double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
@@ -44,9 +44,11 @@ new_context() {
   std::vector<int> dev(n);
   for (int r = 0; r < n; ++r) dev[r] = first + r;
   epv_multi *c = nullptr;
+  const double t0 = now_s();                 // (CUDA initialisation + context creation: the process's first CUDA call)
   if (epv_multi_create(&c, n, dev.data()) != 0 || !c)
     throw std::runtime_error("epievo_b200: no usable CUDA device(s) (EPIEVO_B200_DEVICE / EPIEVO_B200_GPUS; "
                              "there is no CPU fallback)");
+  phase_clock.create += now_s() - t0;
   return c;
 }
 
