@@ -39,13 +39,34 @@ __host__ __device__ constexpr bool mh_defer(int maxn) { return maxn <= 16; }
 
 __device__ __forceinline__ int stage_header_words(int n_br) { return (n_br + 3) >> 2; }
 
-// CTAs per SM the update kernel is compiled for (register budget 65536 / (128 x this)).
-// Measured ms per pass at 3 / 4 / 5: 8-leaf tree (MAXN 16) 6.1 / 5.5 / 6.5; 4-branch test tree
-// (MAXN 8) 6.5 / 6.5 / 7.4; 32-leaf tree (MAXN 64) 7.7 / 8.9 / 10.6.
+// CTAs per SM the update kernel is compiled for (register budget 65536 / (threads x this)).
+// Measured ms per pass at 3 / 4 / 5 CTAs of 128 threads: 8-leaf tree (MAXN 16) 6.1 / 5.5 / 6.5; 4-branch
+// test tree (MAXN 8) 6.5 / 6.5 / 7.4; 32-leaf tree (MAXN 64) 7.7 / 8.9 / 10.6.
+//
+// Threads per CTA.  The halo-free main launch runs ONE large CTA per SM instead of 4 (3) CTAs of 128
+// threads: the 16 (12) warps of an SM then start their site updates together and walk the ~190 KB routine
+// roughly in phase, so they share the instruction cache -- with four CTAs at four different places of the
+// routine, instruction fetch was the largest stall of the test tree's pass (no_instruction 3.1 cycles per
+// issue against 0.3 with one CTA of 512, ncu profiles/r02_update_cta_size_ab.txt) and the pass took 5.60
+// instead of 4.48 ms (8-leaf tree 5.12 -> 4.91, 32-leaf tree 7.49 -> 7.29 at 512; CTAs of 64 / 32 threads:
+// 5.24 / 5.33 on the 8-leaf tree).  The small launches (halo-aware edge groups, overflow list) and the
+// lockstep / mix build variants (shared arrays with a 128-column stride) keep 128.
+#ifndef EPV_MH_T16
+#define EPV_MH_T16 512        // main launch, trees up to 16 nodes
+#endif
+#ifndef EPV_MH_T64
+#define EPV_MH_T64 512        // main launch, trees up to 64 nodes (384 x 1 at 156 registers measured slower: 7.64 vs 7.28 ms)
+#endif
+__host__ __device__ constexpr int mh_impl(int maxn);
+__host__ __device__ constexpr int mh_threads(int maxn, bool halo) {
+  return (halo || maxn > 64 || mh_impl(maxn) != 0) ? MH_THREADS : (maxn <= 16 ? EPV_MH_T16 : EPV_MH_T64);
+}
 #ifdef EPV_MH_MINBLOCKS
-__host__ __device__ constexpr int mh_minblocks(int) { return EPV_MH_MINBLOCKS; }
+__host__ __device__ constexpr int mh_minblocks(int, bool) { return EPV_MH_MINBLOCKS; }
 #else
-__host__ __device__ constexpr int mh_minblocks(int maxn) { return maxn <= 16 ? 4 : 3; }
+__host__ __device__ constexpr int mh_minblocks(int maxn, bool halo) {
+  return (maxn <= 16 ? 512 : 384)/mh_threads(maxn, halo) > 0 ? (maxn <= 16 ? 512 : 384)/mh_threads(maxn, halo) : 1;
+}
 #endif
 
 // The lockstep routine (mh_lock.cuh: branch loop warp-uniform, table-driven single-interval branches)
@@ -81,9 +102,9 @@ __host__ __device__ constexpr int mh_qcap(int maxn) { return maxn <= 16 ? 8 : ma
 // 14 % of its stall cycles).  !DEFER: the full routine -- flat, then the generic per-branch code,
 // then a rerun with a global scratch slot -- all decisions depend on the site's data only, so a
 // site gets the same result whichever launch takes it.
-// Shared memory of the update kernel, in this order: jump queue [MH_THREADS*QCAP] QSlot, prefix counts
-// [MH_THREADS] int, then (lockstep routine, trees up to 64 nodes) TreeTab [n_nodes], BranchTab [n_nodes],
-// jump counts per node u16 [n_nodes][MH_THREADS], q of the internal nodes f64 [2*slots][MH_THREADS].
+// Shared memory of the update kernel, in this order: jump queue [THREADS*QCAP] QSlot, prefix counts
+// [THREADS] int, then (lockstep routine, trees up to 64 nodes) TreeTab [n_nodes], BranchTab [n_nodes],
+// jump counts per node u16 [n_nodes][THREADS], q of the internal nodes f64 [2*slots][THREADS].
 #ifndef EPV_JBASE_SMEM
 #define EPV_JBASE_SMEM 0
 #endif
@@ -91,19 +112,19 @@ struct MhShared {
   QSlot *queue; int *excl; TreeTab *tt; BranchTab *bt; uint16_t *pn; double *q; uint16_t *poff;
   const uint64_t *jbase;
 };
-template <int MAXN>
+template <int MAXN, int THREADS>
 __host__ __device__ inline size_t mh_smem_layout(int n_nodes, int q_slots, size_t *off /*[7]*/) {
   size_t at = 0;
-  off[0] = at; at += (size_t)MH_THREADS*mh_qcap(MAXN)*sizeof(QSlot);
-  off[1] = at; at += (size_t)MH_THREADS*sizeof(int);
+  off[0] = at; at += (size_t)THREADS*mh_qcap(MAXN)*sizeof(QSlot);
+  off[1] = at; at += (size_t)THREADS*sizeof(int);
   if (mh_lock(MAXN)) {
     at = (at + 15) & ~(size_t)15;
     off[2] = at; at += (size_t)n_nodes*sizeof(TreeTab);
     off[3] = at; at += (size_t)n_nodes*sizeof(BranchTab);
-    off[4] = at; at += (size_t)n_nodes*MH_THREADS*sizeof(uint16_t);
+    off[4] = at; at += (size_t)n_nodes*THREADS*sizeof(uint16_t);
     at = (at + 15) & ~(size_t)15;
-    off[5] = at; at += (size_t)2*q_slots*MH_THREADS*sizeof(double);
-    off[6] = at; if (mh_impl(MAXN) == 2) at += (size_t)n_nodes*MH_THREADS*sizeof(uint16_t);
+    off[5] = at; at += (size_t)2*q_slots*THREADS*sizeof(double);
+    off[6] = at; if (mh_impl(MAXN) == 2) at += (size_t)n_nodes*THREADS*sizeof(uint16_t);
   }
   else off[2] = off[3] = off[4] = off[5] = off[6] = at;
   return at;
@@ -242,10 +263,10 @@ mh_update_group(const PassArgs &a, const ModelParams &s_mp, const CtxTables &s_t
         int k = 0;
         for (int bi = 0; bi < 4*hw; ++bi) {
           uint16_t n = 0;
-          if (bi < n_br) n = local_pn ? pn[bi + 1] : (((propmask >> (bi + 1)) & 1) ? sh.pn[(bi + 1)*MH_THREADS + t] : 0);
+          if (bi < n_br) n = local_pn ? pn[bi + 1] : (((propmask >> (bi + 1)) & 1) ? sh.pn[(bi + 1)*mh_threads(MAXN, HALO) + t] : 0);
           cnt[bi] = n;
           if (MIX && !local_pn && n) {                 // rows are not in branch order in pj: gather
-            const double *src = pr.pj + sh.poff[(bi + 1)*MH_THREADS + t];
+            const double *src = pr.pj + sh.poff[(bi + 1)*mh_threads(MAXN, HALO) + t];
             for (int x = 0; x < n; ++x) blob[hw + k++] = src[x];
           }
         }
@@ -261,22 +282,23 @@ mh_update_group(const PassArgs &a, const ModelParams &s_mp, const CtxTables &s_t
 // and (b) the overflow list of the main launch (a.list_mode; grid-stride over the list, whose
 // length is only known on the device).
 template <int MAXN, int MAXJ, bool HALO, bool DEFER, bool QSMEM>
-__global__ void __launch_bounds__(MH_THREADS, mh_minblocks(MAXN))
+__global__ void __launch_bounds__(mh_threads(MAXN, HALO), mh_minblocks(MAXN, HALO))
 mh_update_kernel(const PassArgs a, int q_slots) {
+  constexpr int MT = mh_threads(MAXN, HALO);
   __shared__ ModelParams s_mp;
   __shared__ CtxTables s_tb;
   extern __shared__ __align__(16) unsigned char s_dyn[];
   const int t = threadIdx.x;
 #if EPV_JBASE_SMEM
   __shared__ uint64_t s_jbase[MAXN];
-  for (int i = t; i < a.tree.n_nodes - 1; i += MH_THREADS) s_jbase[i] = a.in.jbase[i];
+  for (int i = t; i < a.tree.n_nodes - 1; i += MT) s_jbase[i] = a.in.jbase[i];
 #endif
   if (t == 0) s_mp = a.mp;
   fill_tables(a.mp, s_tb, t);
   MhShared sh;
   {
     size_t off[7];
-    mh_smem_layout<MAXN>(a.tree.n_nodes, q_slots, off);
+    mh_smem_layout<MAXN, MT>(a.tree.n_nodes, q_slots, off);
     sh.queue = reinterpret_cast<QSlot *>(s_dyn + off[0]); sh.excl = reinterpret_cast<int *>(s_dyn + off[1]);
     sh.tt = reinterpret_cast<TreeTab *>(s_dyn + off[2]); sh.bt = reinterpret_cast<BranchTab *>(s_dyn + off[3]);
     sh.pn = reinterpret_cast<uint16_t *>(s_dyn + off[4]); sh.q = reinterpret_cast<double *>(s_dyn + off[5]);
@@ -289,11 +311,11 @@ mh_update_kernel(const PassArgs a, int q_slots) {
   }
   __syncthreads();
   if (mh_lock(MAXN)) {
-    fill_lock_tables(s_mp, s_tb, a.tree, sh.tt, sh.bt, t, MH_THREADS);
+    fill_lock_tables(s_mp, s_tb, a.tree, sh.tt, sh.bt, t, MT);
     __syncthreads();
   }
   if (!HALO) {
-    uint64_t gi = (uint64_t)blockIdx.x*MH_THREADS + t;
+    uint64_t gi = (uint64_t)blockIdx.x*MT + t;
     if (a.reverse && gi < a.g_count) gi = a.g_count - 1 - gi;
     const uint64_t g = gi >= a.g_count ? a.n_groups                // group of sites 3g..3g+2
                                        : a.g_first + gi + (gi >= a.g_split ? a.g_skip : 0);
@@ -301,9 +323,9 @@ mh_update_kernel(const PassArgs a, int q_slots) {
   }
   else {
     const uint64_t n_items = a.list_mode ? (uint64_t)a.ovf_list[0] : a.g_count;
-    const uint64_t stride = (uint64_t)gridDim.x*MH_THREADS;
+    const uint64_t stride = (uint64_t)gridDim.x*MT;
     // (trip count uniform within a warp: the routine is warp-synchronous)
-    for (uint64_t base = (uint64_t)blockIdx.x*MH_THREADS; base + (uint64_t)(t & ~31) < n_items; base += stride) {
+    for (uint64_t base = (uint64_t)blockIdx.x*MT; base + (uint64_t)(t & ~31) < n_items; base += stride) {
       const uint64_t gi = base + t;
       uint64_t g = a.n_groups;
       if (gi < n_items) g = a.list_mode ? (uint64_t)a.ovf_list[1 + gi] : a.g_first + gi + (gi >= a.g_split ? a.g_skip : 0);
@@ -728,25 +750,26 @@ edge_split(const PassArgs &a, uint64_t &g_lo, uint64_t &g_hi) {
   g_hi = g_hi < a.n_groups ? g_hi : a.n_groups;
 }
 
-// Shared memory per CTA that still lets mh_minblocks(MAXN) CTAs share an SM (227 KB usable, 1 KB
+// Shared memory per CTA that still lets mh_minblocks(MAXN, HALO) CTAs share an SM (227 KB usable, 1 KB
 // reserved per CTA, ~0.4 KB static).
-template <int MAXN>
-static size_t smem_budget() { return (size_t)(232448 - 1024*mh_minblocks(MAXN))/mh_minblocks(MAXN) - 512; }
+template <int MAXN, bool HALO>
+static size_t smem_budget() { return (size_t)(232448 - 1024*mh_minblocks(MAXN, HALO))/mh_minblocks(MAXN, HALO) - 512; }
 
 template <int MAXN, int MAXJ, bool HALO, bool DEFER>
 static void
 launch_variant(const PassArgs &a, unsigned blocks, cudaStream_t st) {
+  constexpr int MT = mh_threads(MAXN, HALO);
   size_t off[7];
-  const bool qsmem = EPV_MH_QSMEM && mh_lock(MAXN) && mh_smem_layout<MAXN>(a.tree.n_nodes, a.q_slots, off) <= smem_budget<MAXN>();
+  const bool qsmem = EPV_MH_QSMEM && mh_lock(MAXN) && mh_smem_layout<MAXN, MT>(a.tree.n_nodes, a.q_slots, off) <= smem_budget<MAXN, HALO>();
   if (qsmem) {
-    const size_t smem = mh_smem_layout<MAXN>(a.tree.n_nodes, a.q_slots, off);
+    const size_t smem = mh_smem_layout<MAXN, MT>(a.tree.n_nodes, a.q_slots, off);
     cudaFuncSetAttribute(mh_update_kernel<MAXN, MAXJ, HALO, DEFER, mh_lock(MAXN)>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    mh_update_kernel<MAXN, MAXJ, HALO, DEFER, mh_lock(MAXN)><<<blocks, MH_THREADS, smem, st>>>(a, a.q_slots);
+    mh_update_kernel<MAXN, MAXJ, HALO, DEFER, mh_lock(MAXN)><<<blocks, MT, smem, st>>>(a, a.q_slots);
   }
   else {
-    const size_t smem = mh_smem_layout<MAXN>(a.tree.n_nodes, 0, off);
+    const size_t smem = mh_smem_layout<MAXN, MT>(a.tree.n_nodes, 0, off);
     cudaFuncSetAttribute(mh_update_kernel<MAXN, MAXJ, HALO, DEFER, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    mh_update_kernel<MAXN, MAXJ, HALO, DEFER, false><<<blocks, MH_THREADS, smem, st>>>(a, 0);
+    mh_update_kernel<MAXN, MAXJ, HALO, DEFER, false><<<blocks, MT, smem, st>>>(a, 0);
   }
 }
 
@@ -766,7 +789,7 @@ launch_interior_t(const PassArgs &a0, cudaStream_t st) {
   const uint64_t defer_min = env ? strtoull(env, nullptr, 10) : (1ull << 20);
   const bool defer = mh_defer(MAXN) && g_hi - g_lo >= defer_min;
   a.g_first = g_lo; a.g_count = a.g_split = g_hi - g_lo; a.g_skip = 0;
-  const unsigned blocks = (unsigned)((a.g_count + MH_THREADS - 1)/MH_THREADS);
+  const unsigned blocks = (unsigned)((a.g_count + mh_threads(MAXN, false) - 1)/mh_threads(MAXN, false));
   if (defer) launch_variant<MAXN, MAXJ, false, mh_defer(MAXN)>(a, blocks, st);
   else launch_variant<MAXN, MAXJ, false, false>(a, blocks, st);
   if (!defer) return 1;
@@ -785,7 +808,7 @@ launch_edge_t(const PassArgs &a0, cudaStream_t st) {
   const uint64_t n_edge = g_lo + (a.n_groups - g_hi);
   if (!n_edge) return 0;
   a.g_first = 0; a.g_split = g_lo; a.g_skip = g_hi - g_lo; a.g_count = n_edge;
-  launch_variant<MAXN, MAXJ, true, false>(a, (unsigned)((n_edge + MH_THREADS - 1)/MH_THREADS), st);
+  launch_variant<MAXN, MAXJ, true, false>(a, (unsigned)((n_edge + mh_threads(MAXN, true) - 1)/mh_threads(MAXN, true)), st);
   return 1;
 }
 
