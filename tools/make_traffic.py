@@ -44,7 +44,7 @@ def main():
         "traffic_bytes_per_launch": upd["dram_bytes_read"] + upd["dram_bytes_write"],
         "issue_active_pct": upd["issue_active_pct"], "lanes_per_inst": upd["lanes_per_inst"],
         "warps_active_pct": upd["warps_active_pct"],
-        "source": "ncu --set full --clock-control none, one launch each (run_gpu_final.sh); summaries in "
+        "source": "ncu --set full --clock-control none, one launch each (tools/sessions/run_gpu_final.sh, run_gpu_final2.sh); summaries in "
                   "profiles/r02_ncu_summary_final.txt",
         "update_kernel": upd,
         "other_kernels": {"csr_rebuild_kernel": reb, "suffstats_tile_kernel": jd},
