@@ -4,8 +4,9 @@
 
 namespace epv {
 
-constexpr int MH_THREADS = 128;                 // groups (of 3 sites) per tile
-constexpr int MH_TILE_SITES = 3*MH_THREADS;
+constexpr int MH_THREADS = 128;                 // update kernel: groups (of 3 sites) per CTA of the small launches (edge
+                                                // groups, overflow list) and of trees wider than 64 nodes; the main
+                                                // launch runs one large CTA per SM (mh_threads(), kernels_mh.cu)
 constexpr int RB_THREADS = 256;                 // rebuild kernel: 4 CSR rows per thread
 constexpr int RB_TILE_ROWS = 4*RB_THREADS;
 
