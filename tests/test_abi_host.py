@@ -133,3 +133,26 @@ def test_multi_partition_matches_the_python_driver():
         assert b[0] == 0 and e[-1] == n and all(int(x) % 3 == 0 for x in b)
     b, e = np.zeros(4, np.uint64), np.zeros(4, np.uint64)
     assert lib.epv_multi_partition(20, 4, b.ctypes.data_as(L.u64p), e.ctypes.data_as(L.u64p)) != 0   # < 6 sites per shard
+
+
+@pytest.mark.parametrize("exe,args", [
+    ("epievo_est_params_histories_b200", ["-s", "1", "-i", "1", "-o", "{tmp}/o.paths", "-p", "{tmp}/o.param",
+                                          "{cli}/test.param", "{cli}/tree.nwk", "{cli}/sim.paths"]),
+    ("epievo_est_complete_b200", ["-o", "{tmp}/c.param", "{cli}/test.param", "{cli}/tree.nwk", "{cli}/sim.paths"]),
+])
+def test_dropin_programs_fail_the_reference_way_without_a_gpu(tmp_path, exe, args):
+    """The reference's own main()s, compiled unchanged against the drop-in (integration/Makefile): without a
+    CUDA device they print the library's message and return EXIT_FAILURE through the reference's own
+    `catch (const std::exception &)` -- they neither crash nor compute anything on the host."""
+    import subprocess
+
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    p = os.path.join(ROOT, "integration", "_build", exe)
+    if not os.path.exists(p):
+        pytest.skip("integration/_build not built (make -C integration needs /root/reference)")
+    r = subprocess.run([p] + [a.format(tmp=tmp_path, cli=CLI) for a in args], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 1, (r.returncode, r.stderr[-500:])
+    assert "no usable CUDA device" in r.stderr and "no CPU fallback" in r.stderr
+    assert not os.path.exists(os.path.join(str(tmp_path), "c.param")) or os.path.getsize(os.path.join(str(tmp_path), "c.param")) == 0
