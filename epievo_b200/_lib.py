@@ -108,6 +108,7 @@ SIGNATURES = {
     "epv_pathfile_node_name": (C.c_char_p, [C.c_void_p, u64]),
     "epv_pathfile_free": (None, [C.c_void_p]),
     "epv_pathfile_write": (C.c_int, [C.c_char_p, u64, u64, C.POINTER(C.c_char_p), u8p, u64p, dp, dp, C.c_int]),
+    "epv_pathfile_write_binary": (C.c_int, [C.c_char_p, u64, u64, C.POINTER(C.c_char_p), u8p, u64p, dp, dp, C.c_int]),
     "epv_io_last_error": (C.c_char_p, []),
     "epv_launch_count": (u64, [ctx_p]),
     "epv_recovery_count": (u64, [ctx_p]),

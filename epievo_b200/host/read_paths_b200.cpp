@@ -5,6 +5,7 @@
  * BEFORE the reference's Path.o with -Wl,--allow-multiple-definition (the first
  * definition wins); everything else of Path.o stays the reference's. */
 #include <stdexcept>
+#include <sys/stat.h>
 #include <string>
 #include <vector>
 
@@ -16,8 +17,22 @@ read_paths(const std::string &path_file, std::vector<std::string> &node_names,
            std::vector<std::vector<Path> > &paths) {
   epv_pathfile *f = nullptr;
   uint64_t n_sites = 0, n_nodes = 0, n_jumps = 0;
-  if (epv_pathfile_read(path_file.c_str(), 0, &f, &n_sites, &n_nodes, &n_jumps))
-    throw std::runtime_error(epv_io_last_error());
+  // optional binary sidecar (epv_pathfile_write_binary, tools/paths_sidecar.py): <file>.epvb is read instead of
+  // the text when it is not older than the text file -- seconds instead of minutes at 1e8 sites
+  std::string source = path_file;
+  {
+    struct stat st_txt, st_bin;
+    const std::string side = path_file + ".epvb";
+    if (stat(side.c_str(), &st_bin) == 0 && stat(path_file.c_str(), &st_txt) == 0 &&
+        (st_bin.st_mtim.tv_sec > st_txt.st_mtim.tv_sec ||
+         (st_bin.st_mtim.tv_sec == st_txt.st_mtim.tv_sec && st_bin.st_mtim.tv_nsec >= st_txt.st_mtim.tv_nsec)))
+      source = side;
+  }
+  if (epv_pathfile_read(source.c_str(), 0, &f, &n_sites, &n_nodes, &n_jumps)) {
+    // a damaged sidecar must not hide a good text file
+    if (source == path_file || epv_pathfile_read(path_file.c_str(), 0, &f, &n_sites, &n_nodes, &n_jumps))
+      throw std::runtime_error(epv_io_last_error());
+  }
   std::vector<uint8_t> init(n_sites*n_nodes);
   std::vector<uint64_t> off(n_sites*n_nodes + 1);
   std::vector<double> jumps(n_jumps + 1), tot(n_nodes);

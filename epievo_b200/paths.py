@@ -223,6 +223,23 @@ def write_paths_native(path_file: str, ps: PathSet, node_names: Sequence[str] = 
         raise RuntimeError(lib.epv_io_last_error().decode())
 
 
+def write_paths_binary(path_file: str, ps: PathSet, node_names: Sequence[str] = (),
+                       n_threads: int = 0) -> None:
+    """The binary sidecar form of a local-paths file (epv_pathfile_write_binary; read_paths_native reads both
+    forms, the read_paths drop-in prefers `<file>.epvb` next to a text file that is not newer)."""
+    import ctypes as C
+
+    from . import _lib as L
+    lib = L.load()
+    names = list(node_names) or list(ps.node_names) or ["node_%d" % i for i in range(ps.n_nodes)]
+    arr = (C.c_char_p * ps.n_nodes)(*[n.encode() for n in names])
+    j = ps.jumps if len(ps.jumps) else np.zeros(1)
+    if lib.epv_pathfile_write_binary(path_file.encode(), ps.n_sites, ps.n_nodes, arr,
+                                     ps.init_state.ctypes.data_as(L.u8p), ps.row_off.ctypes.data_as(L.u64p),
+                                     j.ctypes.data_as(L.dp), ps.tot_time.ctypes.data_as(L.dp), n_threads):
+        raise RuntimeError(lib.epv_io_last_error().decode())
+
+
 def _fmt(x: float) -> str:
     # operator<<(ostream, Path) sets precision(max_digits10) = 17 significant digits in
     # the default (%g-like) float format (Path.cpp:62-71).

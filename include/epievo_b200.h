@@ -358,6 +358,16 @@ int epv_pathfile_write(const char *filename, uint64_t n_sites, uint64_t n_nodes,
                        const char *const *node_names, const uint8_t *init_state,
                        const uint64_t *row_off, const double *jumps,
                        const double *tot_time, int n_threads);
+/* The same content as a binary file (2 bytes per row + 8 per jump instead of ~22 bytes of text per row; the
+ * "optional binary CSR sidecar" of SURVEY 8f-1 -- no counterpart in the reference): "EPVPATH1" header with the
+ * sizes and a checksum, node names, tot_time, one u16 per row (bit 15 = init_state, bits 0-14 = jumps of the
+ * row, hence at most 32767 jumps per row), the jump times.  epv_pathfile_read recognises the magic, so every
+ * reader of the text form reads this one too; a truncated or altered file is an error, never partial data.
+ * host/read_paths_b200.cpp (the read_paths drop-in) prefers <file>.epvb when it is not older than <file>. */
+int epv_pathfile_write_binary(const char *filename, uint64_t n_sites, uint64_t n_nodes,
+                              const char *const *node_names, const uint8_t *init_state,
+                              const uint64_t *row_off, const double *jumps,
+                              const double *tot_time, int n_threads);
 const char *epv_io_last_error(void);
 
 /* ---- instrumentation ------------------------------------------------------------- */

@@ -12,7 +12,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [ROOT, os.path.join(ROOT, "tests")]
 
 import cpu_libs  # noqa: E402
-from epievo_b200.paths import read_paths_native, write_paths_native  # noqa: E402
+from epievo_b200.paths import read_paths_native, write_paths_binary, write_paths_native  # noqa: E402
 from epievo_b200.synthetic import simulate_paths  # noqa: E402
 from synth import TEST_PARAMS, ref_test_tree  # noqa: E402
 
@@ -33,6 +33,13 @@ out = {"n_sites": n, "n_branches": ps.n_nodes - 1, "file_mb": size / 1e6,
        "threads": threads or os.cpu_count(),
        "native_write_s": tw, "native_read_s": tr,
        "native_write_mb_s": size / 1e6 / tw, "native_read_mb_s": size / 1e6 / tr}
+# the binary sidecar of the same content
+b = os.path.join(d, "a.epvb")
+t0 = time.perf_counter(); write_paths_binary(b, ps, n_threads=threads); tbw = time.perf_counter() - t0
+t0 = time.perf_counter(); back = read_paths_native(b, threads); tbr = time.perf_counter() - t0
+assert back.same_as(ps)
+out.update({"binary_mb": os.path.getsize(b) / 1e6, "binary_write_s": tbw, "binary_read_s": tbr})
+os.remove(b)
 if cpu_libs.ref_available():
     ref = cpu_libs.ref()
     got, sec = ref.read_paths_file(f, timing=True)
